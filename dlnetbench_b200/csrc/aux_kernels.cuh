@@ -1,0 +1,86 @@
+// aux_kernels.cuh — compute-emulation spin kernel and test/bench helper kernels.
+// Included by runtime.cu only.
+#pragma once
+#include "kernels.cuh"
+
+namespace dlnb {
+
+// ----------------------------------------------------------------------------
+// Emulated compute: spin on %globaltimer for `ns` nanoseconds.
+// ----------------------------------------------------------------------------
+__global__ void spin_kernel(unsigned long long ns) {
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+        const unsigned long long el = globaltimer_ns() - t0;
+        if (el >= ns) break;
+        const unsigned long long left = ns - el;
+        // back off while far from the deadline so the SM's issue slots stay free
+        if (left > 4000) __nanosleep(left > 64000 ? 16000 : (unsigned)(left >> 2));
+    }
+}
+
+// ----------------------------------------------------------------------------
+// Test / bench helpers
+// ----------------------------------------------------------------------------
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352du;
+    x ^= x >> 15; x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
+}
+// value of element i of rank r's buffer, as fp32 before rounding to the dtype
+__host__ __device__ __forceinline__ float pattern_value(int kind, uint64_t seed, int r, uint64_t i) {
+    if (kind == 1) {
+        const uint64_t h = i * 2654435761ull + (uint64_t)r * 40503ull;
+        return (float)((int)(h % 17ull) - 8);
+    } else if (kind == 2) {
+        uint32_t h = mix32((uint32_t)i ^ mix32((uint32_t)(i >> 32) + 0x9e3779b9u * (uint32_t)(r + 1) +
+                                               (uint32_t)seed));
+        return (float)((int)(h >> 8) - (1 << 23)) * (1.0f / 8388608.0f);
+    }
+    return 0.0f;
+}
+
+template <typename T>
+__global__ void fill_kernel(T *p, size_t n, int kind, uint64_t seed, int r) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = Elem<T>::from_f(pattern_value(kind, seed, r, i));
+}
+
+struct RankList { int r[MAXR]; int n; };
+
+template <typename T>
+__global__ void verify_sum_kernel(const T *p, size_t n, size_t elem_off, int kind, uint64_t seed,
+                                  RankList rl, unsigned long long *mismatches) {
+    unsigned long long bad = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        // each rank's element is first rounded to T (that is what the buffer held)
+        float acc = Elem<T>::to_f(Elem<T>::from_f(pattern_value(kind, seed, rl.r[0], elem_off + i)));
+        for (int k = 1; k < rl.n; ++k)
+            acc += Elem<T>::to_f(Elem<T>::from_f(pattern_value(kind, seed, rl.r[k], elem_off + i)));
+        const T want = rl.n == 1 ? Elem<T>::from_f(pattern_value(kind, seed, rl.r[0], elem_off + i))
+                                 : Elem<T>::from_f(acc);
+        const T got = p[i];
+        bool same;
+        if (sizeof(T) == 4) same = *(const uint32_t *)&want == *(const uint32_t *)&got;
+        else same = *(const uint16_t *)&want == *(const uint16_t *)&got;
+        bad += same ? 0 : 1;
+    }
+    for (int o = 16; o > 0; o >>= 1) bad += __shfl_down_sync(0xffffffffu, bad, o);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(mismatches, bad);
+}
+
+__global__ void checksum_kernel(const uint32_t *p, size_t nwords, unsigned long long *out) {
+    unsigned long long s = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x)
+        s += (unsigned long long)mix32(p[i] + (uint32_t)i * 0x9e3779b9u);
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(out, s);
+}
+
+__global__ void flush_kernel(uint4 *p, size_t nvec, uint32_t tag) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = make_uint4(tag, tag, tag, tag);
+}
+
+} // namespace dlnb

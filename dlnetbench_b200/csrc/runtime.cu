@@ -1,0 +1,947 @@
+// runtime.cu — host side of libdlnb.so: the C ABI declared in include/dlnb.h.
+//
+// One process per GPU. Owns: the rendezvous (bootstrap.cpp), the symmetric arena
+// (cuMem VMM chunks exported as POSIX fds and mapped by every peer), two ordered
+// streams (emulated compute, communication) plus a copy stream, per-slot events,
+// communicators (rank lists + flag rows + control block) and the kernel launches.
+//
+// Reference counterparts: cpp/proxy_classes.hpp (CCLCommunicator :135-253, Tensor
+// :381-444), cpp/utils.hpp:74-117 (set_local_device), cpp/data_parallel/dp.cpp:166-232.
+#include "../../include/dlnb.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "aux_kernels.cuh"
+#include "bootstrap.hpp"
+#include "launch.hpp"
+
+using namespace dlnb;
+
+// ---------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------
+static std::string g_err;
+static int fail(const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+#define CU_TRY(expr)                                                                               \
+    do {                                                                                           \
+        cudaError_t e_ = (expr);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// driver API entry points, resolved through the runtime so that libdlnb.so has no
+// link-time dependency on libcuda (it must load on a box without a driver).
+// ---------------------------------------------------------------------------
+struct Drv {
+    CUresult (*MemGetAllocationGranularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags);
+    CUresult (*MemAddressReserve)(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long);
+    CUresult (*MemAddressFree)(CUdeviceptr, size_t);
+    CUresult (*MemCreate)(CUmemGenericAllocationHandle *, size_t, const CUmemAllocationProp *, unsigned long long);
+    CUresult (*MemRelease)(CUmemGenericAllocationHandle);
+    CUresult (*MemExportToShareableHandle)(void *, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long);
+    CUresult (*MemImportFromShareableHandle)(CUmemGenericAllocationHandle *, void *, CUmemAllocationHandleType);
+    CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long);
+    CUresult (*MemUnmap)(CUdeviceptr, size_t);
+    CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t);
+    CUresult (*GetErrorString)(CUresult, const char **);
+    bool ok = false;
+};
+static Drv drv;
+
+static int load_driver() {
+    if (drv.ok) return 0;
+#define DLNB_SYM(field, name)                                                                      \
+    do {                                                                                           \
+        void *p = nullptr;                                                                         \
+        cudaDriverEntryPointQueryResult q;                                                         \
+        cudaError_t e = cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q);                  \
+        if (e != cudaSuccess || !p) return fail("driver symbol %s not available", name);           \
+        drv.field = (decltype(drv.field))p;                                                        \
+    } while (0)
+    DLNB_SYM(MemGetAllocationGranularity, "cuMemGetAllocationGranularity");
+    DLNB_SYM(MemAddressReserve, "cuMemAddressReserve");
+    DLNB_SYM(MemAddressFree, "cuMemAddressFree");
+    DLNB_SYM(MemCreate, "cuMemCreate");
+    DLNB_SYM(MemRelease, "cuMemRelease");
+    DLNB_SYM(MemExportToShareableHandle, "cuMemExportToShareableHandle");
+    DLNB_SYM(MemImportFromShareableHandle, "cuMemImportFromShareableHandle");
+    DLNB_SYM(MemMap, "cuMemMap");
+    DLNB_SYM(MemUnmap, "cuMemUnmap");
+    DLNB_SYM(MemSetAccess, "cuMemSetAccess");
+    DLNB_SYM(GetErrorString, "cuGetErrorString");
+#undef DLNB_SYM
+    drv.ok = true;
+    return 0;
+}
+static const char *drv_err(CUresult r) {
+    const char *s = nullptr;
+    if (drv.GetErrorString) drv.GetErrorString(r, &s);
+    return s ? s : "unknown driver error";
+}
+#define DRV_TRY(expr)                                                                              \
+    do {                                                                                           \
+        CUresult r_ = (expr);                                                                      \
+        if (r_ != CUDA_SUCCESS)                                                                    \
+            return fail("%s failed: %s (%s:%d)", #expr, drv_err(r_), __FILE__, __LINE__);          \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// state
+// ---------------------------------------------------------------------------
+enum ArenaKind { ARENA_LOCAL = 0, ARENA_VMM = 1, ARENA_IPC = 2 };
+
+struct Chunk {
+    char *local = nullptr;
+    size_t size = 0, used = 0;
+    char *peer[MAXR] = {};                   // my mapping of world rank p's copy
+    CUmemGenericAllocationHandle handle = 0; // VMM only
+    std::vector<CUmemGenericAllocationHandle> imported;
+};
+
+struct dlnb_comm {
+    int id = 0, n = 1, me = 0, dtype = DLNB_F32, num_slots = 1;
+    int ranks[MAXR] = {};
+    std::vector<cudaEvent_t> ev_start, ev_end;
+    std::vector<char> slot_used;
+    long ctas = 0, threads = 512, algo = DLNB_ALGO_AUTO, twoshot_min_bytes = 256 * 1024, timeout_ms = 30000;
+};
+
+static constexpr int MAX_COMMS = 64;
+static constexpr size_t FLAG_BYTES_PER_COMM = (size_t)MAX_FLAG_CTAS * FLAG_ROW * sizeof(uint32_t);
+
+struct State {
+    bool inited = false;
+    int rank = 0, world = 1, device = 0, sms = 0;
+    ArenaKind kind = ARENA_LOCAL;
+    Bootstrap boot;
+    cudaStream_t s_compute = nullptr, s_comm = nullptr, s_copy = nullptr;
+    cudaEvent_t ev_join = nullptr, ev_copy = nullptr, ev_iter0 = nullptr, ev_iter1 = nullptr, ev_tmp0 = nullptr,
+                ev_tmp1 = nullptr;
+    bool compute_dirty = false, copy_dirty = false;
+    // arena
+    std::vector<Chunk> chunks;
+    size_t gran = 2u << 20, min_chunk = 256u << 20, va_size = 0, va_used = 0;
+    CUdeviceptr window[MAXR] = {};
+    size_t bytes_in_use = 0;
+    // flags / control
+    char *flag_area = nullptr; // symmetric: MAX_COMMS * FLAG_BYTES_PER_COMM
+    CommCtl *ctl = nullptr;    // symmetric allocation too (only used locally)
+    uint32_t *host_error = nullptr, *host_error_dev = nullptr;
+    int next_comm = 0;
+    std::vector<dlnb_comm *> comms;
+    // emulation scratch (single-GPU n-rank mode)
+    uint32_t *emu_flags = nullptr;
+    CommCtl *emu_ctl = nullptr;
+    // spin
+    long spin_ctas = 1, spin_threads = 32, slot_timing = 1;
+    double spin_overhead_us = 0.0, spin_slope = 1.0;
+    // misc
+    uint64_t launches = 0;
+    void *flush_buf = nullptr;
+    size_t flush_bytes = 0;
+    unsigned long long *d_scalar = nullptr; // 8-byte device scratch for verify/checksum
+};
+static State G;
+
+#define NEED_INIT()                                                                                \
+    do {                                                                                           \
+        if (!G.inited) return fail("dlnb_init has not been called");                               \
+    } while (0)
+
+static size_t round_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static size_t dtype_size(int dt) { return dt == DLNB_F32 ? 4 : 2; }
+
+// ---------------------------------------------------------------------------
+// arena
+// ---------------------------------------------------------------------------
+static int arena_grow(size_t need) {
+    Chunk c;
+    const size_t want = std::max(need, G.min_chunk);
+    if (G.kind == ARENA_LOCAL) {
+        c.size = round_up(want, 2u << 20);
+        void *p = nullptr;
+        CU_TRY(cudaMalloc(&p, c.size));
+        c.local = (char *)p;
+        c.peer[0] = c.local;
+        for (int r = 0; r < MAXR; ++r) c.peer[r] = (r == G.rank) ? c.local : nullptr;
+    } else if (G.kind == ARENA_VMM) {
+        c.size = round_up(want, G.gran);
+        if (G.va_used + c.size > G.va_size)
+            return fail("symmetric arena exhausted its %zu GiB of reserved address space", G.va_size >> 30);
+        CUmemAllocationProp prop = {};
+        prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        prop.location.id = G.device;
+        prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+        DRV_TRY(drv.MemCreate(&c.handle, c.size, &prop, 0));
+        int fd = -1;
+        DRV_TRY(drv.MemExportToShareableHandle(&fd, c.handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+        // consistency: every rank must be growing by the same amount
+        std::vector<size_t> sizes((size_t)G.world);
+        std::string e = G.boot.allgather(&c.size, sizeof(size_t), sizes.data());
+        if (!e.empty()) return fail("%s", e.c_str());
+        for (int r = 0; r < G.world; ++r)
+            if (sizes[r] != c.size)
+                return fail("dlnb_symm_alloc is collective: rank %d grows by %zu bytes, rank %d by %zu", G.rank,
+                            c.size, r, sizes[r]);
+        std::vector<int> fds;
+        e = G.boot.exchange_fds(fd, fds);
+        if (!e.empty()) return fail("%s", e.c_str());
+        ::close(fd);
+        CUmemAccessDesc acc = {};
+        acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        acc.location.id = G.device;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        c.imported.assign((size_t)G.world, 0);
+        for (int r = 0; r < G.world; ++r) {
+            CUdeviceptr va = G.window[r] + G.va_used;
+            CUmemGenericAllocationHandle h = c.handle;
+            if (r != G.rank) {
+                DRV_TRY(drv.MemImportFromShareableHandle(&h, (void *)(uintptr_t)fds[r],
+                                                         CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+                c.imported[r] = h;
+            }
+            DRV_TRY(drv.MemMap(va, c.size, 0, h, 0));
+            DRV_TRY(drv.MemSetAccess(va, c.size, &acc, 1));
+            c.peer[r] = (char *)va;
+            ::close(fds[r]);
+        }
+        c.local = c.peer[G.rank];
+        G.va_used += c.size;
+    } else { // ARENA_IPC (diagnostic fallback: cudaMalloc + cudaIpc handles)
+        c.size = round_up(want, 2u << 20);
+        void *p = nullptr;
+        CU_TRY(cudaMalloc(&p, c.size));
+        c.local = (char *)p;
+        cudaIpcMemHandle_t mine;
+        CU_TRY(cudaIpcGetMemHandle(&mine, p));
+        std::vector<cudaIpcMemHandle_t> all((size_t)G.world);
+        std::string e = G.boot.allgather(&mine, sizeof(mine), all.data());
+        if (!e.empty()) return fail("%s", e.c_str());
+        for (int r = 0; r < G.world; ++r) {
+            if (r == G.rank) {
+                c.peer[r] = c.local;
+            } else {
+                void *q = nullptr;
+                CU_TRY(cudaIpcOpenMemHandle(&q, all[r], cudaIpcMemLazyEnablePeerAccess));
+                c.peer[r] = (char *)q;
+            }
+        }
+    }
+    CU_TRY(cudaMemset(c.local, 0, c.size));
+    CU_TRY(cudaDeviceSynchronize());
+    if (G.boot.active()) {
+        std::string e = G.boot.barrier(); // peers' mappings exist before anyone uses them
+        if (!e.empty()) return fail("%s", e.c_str());
+    }
+    G.chunks.push_back(std::move(c));
+    return 0;
+}
+
+static int arena_alloc(size_t bytes, void **out) {
+    const size_t need = round_up(std::max<size_t>(bytes, 1), 1024);
+    if (G.chunks.empty() || G.chunks.back().used + need > G.chunks.back().size) {
+        if (arena_grow(need)) return 1;
+    }
+    Chunk &c = G.chunks.back();
+    *out = c.local + c.used;
+    c.used += need;
+    G.bytes_in_use += need;
+    return 0;
+}
+
+// my mapping of world rank `wr`'s copy of the symmetric allocation holding `p`
+static char *translate(const void *p, int wr) {
+    if (wr == G.rank) return (char *)p;
+    const char *q = (const char *)p;
+    for (const Chunk &c : G.chunks)
+        if (q >= c.local && q < c.local + c.size) return c.peer[wr] ? c.peer[wr] + (q - c.local) : nullptr;
+    return nullptr;
+}
+
+// ---------------------------------------------------------------------------
+// init / finalize
+// ---------------------------------------------------------------------------
+extern "C" const char *dlnb_last_error(void) { return g_err.c_str(); }
+extern "C" const char *dlnb_version(void) { return "dlnb 0.1 (sm_100a)"; }
+extern "C" int dlnb_rank(void) { return G.rank; }
+extern "C" int dlnb_world(void) { return G.world; }
+extern "C" int dlnb_device(void) { return G.device; }
+extern "C" const char *dlnb_arena_kind(void) {
+    return G.kind == ARENA_VMM ? "vmm" : G.kind == ARENA_IPC ? "ipc" : "local";
+}
+extern "C" uint64_t dlnb_launch_count(void) { return G.launches; }
+extern "C" size_t dlnb_symm_bytes_in_use(void) { return G.bytes_in_use; }
+
+extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
+    if (G.inited) return fail("dlnb_init called twice");
+    if (world < 1 || world > MAXR) return fail("world size %d not in 1..%d (one NVSwitch box)", world, MAXR);
+    if (rank < 0 || rank >= world) return fail("rank %d out of range for world %d", rank, world);
+    int ndev = 0;
+    CU_TRY(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) return fail("no CUDA device visible: libdlnb has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail("device %d out of range (%d visible)", device, ndev);
+    CU_TRY(cudaSetDevice(device));
+    CU_TRY(cudaFree(0));
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10 && !getenv("DLNB_ALLOW_ANY_ARCH"))
+        return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major,
+                    prop.minor);
+    G.rank = rank;
+    G.world = world;
+    G.device = device;
+    G.sms = prop.multiProcessorCount;
+
+    if (world > 1) {
+        const char *k = getenv("DLNB_ARENA");
+        G.kind = (k && !strcmp(k, "ipc")) ? ARENA_IPC : ARENA_VMM;
+        std::string e = G.boot.connect(rank, world, session ? session : "default", 120);
+        if (!e.empty()) return fail("%s", e.c_str());
+    } else {
+        G.kind = ARENA_LOCAL;
+    }
+    if (const char *m = getenv("DLNB_CHUNK_MB")) G.min_chunk = (size_t)atol(m) << 20;
+
+    if (G.kind == ARENA_VMM) {
+        if (load_driver()) return 1;
+        CUmemAllocationProp ap = {};
+        ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        ap.location.id = device;
+        ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+        DRV_TRY(drv.MemGetAllocationGranularity(&G.gran, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+        size_t gb = 256;
+        if (const char *v = getenv("DLNB_ARENA_VA_GB")) gb = (size_t)atol(v);
+        G.va_size = gb << 30;
+        for (int r = 0; r < world; ++r) DRV_TRY(drv.MemAddressReserve(&G.window[r], G.va_size, G.gran, 0, 0));
+    }
+
+    int lo = 0, hi = 0;
+    CU_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi)); // lo = least priority (numerically greatest)
+    CU_TRY(cudaStreamCreateWithPriority(&G.s_compute, cudaStreamNonBlocking, lo));
+    CU_TRY(cudaStreamCreateWithPriority(&G.s_comm, cudaStreamNonBlocking, hi));
+    CU_TRY(cudaStreamCreateWithPriority(&G.s_copy, cudaStreamNonBlocking, lo));
+    CU_TRY(cudaEventCreateWithFlags(&G.ev_join, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&G.ev_copy, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreate(&G.ev_iter0));
+    CU_TRY(cudaEventCreate(&G.ev_iter1));
+    CU_TRY(cudaEventCreate(&G.ev_tmp0));
+    CU_TRY(cudaEventCreate(&G.ev_tmp1));
+    CU_TRY(cudaHostAlloc((void **)&G.host_error, sizeof(uint32_t), cudaHostAllocMapped));
+    *G.host_error = 0;
+    CU_TRY(cudaHostGetDevicePointer((void **)&G.host_error_dev, G.host_error, 0));
+    CU_TRY(cudaMalloc((void **)&G.d_scalar, sizeof(unsigned long long)));
+
+    G.inited = true;
+    // first symmetric allocations: flag rows and control blocks of all communicators
+    void *p = nullptr;
+    if (arena_alloc((size_t)MAX_COMMS * FLAG_BYTES_PER_COMM, &p)) { G.inited = false; return 1; }
+    G.flag_area = (char *)p;
+    if (arena_alloc((size_t)MAX_COMMS * sizeof(CommCtl), &p)) { G.inited = false; return 1; }
+    G.ctl = (CommCtl *)p;
+    return 0;
+}
+
+extern "C" int dlnb_finalize(void) {
+    if (!G.inited) return 0;
+    cudaDeviceSynchronize();
+    if (G.boot.active()) G.boot.barrier(); // nobody unmaps while a peer may still touch it
+    for (dlnb_comm *c : G.comms) {
+        if (!c) continue;
+        for (auto e : c->ev_start) cudaEventDestroy(e);
+        for (auto e : c->ev_end) cudaEventDestroy(e);
+        delete c;
+    }
+    G.comms.clear();
+    for (Chunk &c : G.chunks) {
+        if (G.kind == ARENA_VMM) {
+            for (int r = 0; r < G.world; ++r)
+                if (c.peer[r]) drv.MemUnmap((CUdeviceptr)c.peer[r], c.size);
+            for (auto h : c.imported)
+                if (h) drv.MemRelease(h);
+            drv.MemRelease(c.handle);
+        } else if (G.kind == ARENA_IPC) {
+            for (int r = 0; r < G.world; ++r)
+                if (r != G.rank && c.peer[r]) cudaIpcCloseMemHandle(c.peer[r]);
+            if (G.boot.active()) G.boot.barrier();
+            cudaFree(c.local);
+        } else {
+            cudaFree(c.local);
+        }
+    }
+    G.chunks.clear();
+    if (G.kind == ARENA_VMM)
+        for (int r = 0; r < G.world; ++r)
+            if (G.window[r]) drv.MemAddressFree(G.window[r], G.va_size);
+    if (G.emu_flags) cudaFree(G.emu_flags);
+    if (G.emu_ctl) cudaFree(G.emu_ctl);
+    if (G.flush_buf) cudaFree(G.flush_buf);
+    if (G.d_scalar) cudaFree(G.d_scalar);
+    if (G.host_error) cudaFreeHost(G.host_error);
+    cudaStreamDestroy(G.s_compute);
+    cudaStreamDestroy(G.s_comm);
+    cudaStreamDestroy(G.s_copy);
+    cudaEventDestroy(G.ev_join);
+    cudaEventDestroy(G.ev_copy);
+    cudaEventDestroy(G.ev_iter0);
+    cudaEventDestroy(G.ev_iter1);
+    cudaEventDestroy(G.ev_tmp0);
+    cudaEventDestroy(G.ev_tmp1);
+    G.boot.close_all();
+    G = State();
+    return 0;
+}
+
+extern "C" int dlnb_host_barrier(void) {
+    NEED_INIT();
+    std::string e = G.boot.barrier();
+    return e.empty() ? 0 : fail("%s", e.c_str());
+}
+extern "C" int dlnb_host_allgather(const void *in, size_t bytes, void *out) {
+    NEED_INIT();
+    std::string e = G.boot.allgather(in, bytes, out);
+    return e.empty() ? 0 : fail("%s", e.c_str());
+}
+
+extern "C" int dlnb_symm_alloc(size_t bytes, void **ptr) {
+    NEED_INIT();
+    if (!ptr) return fail("dlnb_symm_alloc: null out pointer");
+    return arena_alloc(bytes, ptr);
+}
+extern "C" int dlnb_symm_free(void *) { return 0; }
+
+extern "C" int dlnb_set(const char *key, long value) {
+    if (!strcmp(key, "spin_ctas")) G.spin_ctas = std::max(1L, value);
+    else if (!strcmp(key, "spin_threads")) G.spin_threads = std::min(1024L, std::max(1L, value));
+    else if (!strcmp(key, "slot_timing")) G.slot_timing = value;
+    else return fail("dlnb_set: unknown key %s", key);
+    return 0;
+}
+extern "C" long dlnb_get(const char *key) {
+    if (!strcmp(key, "spin_ctas")) return G.spin_ctas;
+    if (!strcmp(key, "spin_threads")) return G.spin_threads;
+    if (!strcmp(key, "slot_timing")) return G.slot_timing;
+    if (!strcmp(key, "sms")) return G.sms;
+    return -1;
+}
+
+// ---------------------------------------------------------------------------
+// communicators
+// ---------------------------------------------------------------------------
+extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int dtype, dlnb_comm_t *out) {
+    NEED_INIT();
+    if (!ranks || !out) return fail("dlnb_comm_create: null argument");
+    if (nranks < 1 || nranks > MAXR) return fail("dlnb_comm_create: group size %d not in 1..%d", nranks, MAXR);
+    if (dtype < DLNB_F32 || dtype > DLNB_BF16) return fail("dlnb_comm_create: unknown dtype %d", dtype);
+    if (G.next_comm >= MAX_COMMS) return fail("dlnb_comm_create: more than %d communicators", MAX_COMMS);
+    dlnb_comm *c = new dlnb_comm;
+    c->me = -1;
+    for (int i = 0; i < nranks; ++i) {
+        if (ranks[i] < 0 || ranks[i] >= G.world) {
+            delete c;
+            return fail("dlnb_comm_create: rank %d outside world %d", ranks[i], G.world);
+        }
+        c->ranks[i] = ranks[i];
+        if (ranks[i] == G.rank) c->me = i;
+    }
+    if (c->me < 0) {
+        delete c;
+        return fail("dlnb_comm_create: calling rank %d is not in the group", G.rank);
+    }
+    c->id = G.next_comm++;
+    c->n = nranks;
+    c->dtype = dtype;
+    c->num_slots = std::max(1, num_slots);
+    c->ev_start.resize(c->num_slots);
+    c->ev_end.resize(c->num_slots);
+    c->slot_used.assign(c->num_slots, 0);
+    for (int i = 0; i < c->num_slots; ++i) {
+        CU_TRY(cudaEventCreate(&c->ev_start[i]));
+        CU_TRY(cudaEventCreate(&c->ev_end[i]));
+    }
+    if (const char *v = getenv("DLNB_CTAS")) c->ctas = atol(v);
+    if (const char *v = getenv("DLNB_THREADS")) c->threads = atol(v);
+    if (const char *v = getenv("DLNB_ALGO")) c->algo = atol(v);
+    if (const char *v = getenv("DLNB_TWOSHOT_MIN_BYTES")) c->twoshot_min_bytes = atol(v);
+    G.comms.push_back(c);
+    *out = c;
+    return 0;
+}
+extern "C" int dlnb_comm_destroy(dlnb_comm_t c) {
+    if (!c) return 0;
+    for (auto &slot : G.comms)
+        if (slot == c) slot = nullptr;
+    for (auto e : c->ev_start) cudaEventDestroy(e);
+    for (auto e : c->ev_end) cudaEventDestroy(e);
+    delete c;
+    return 0;
+}
+extern "C" int dlnb_comm_rank(dlnb_comm_t c) { return c ? c->me : -1; }
+extern "C" int dlnb_comm_size(dlnb_comm_t c) { return c ? c->n : -1; }
+extern "C" int dlnb_comm_set(dlnb_comm_t c, const char *key, long value) {
+    if (!c) return fail("dlnb_comm_set: null communicator");
+    if (!strcmp(key, "ctas")) c->ctas = value;
+    else if (!strcmp(key, "threads")) c->threads = value;
+    else if (!strcmp(key, "algo")) c->algo = value;
+    else if (!strcmp(key, "twoshot_min_bytes")) c->twoshot_min_bytes = value;
+    else if (!strcmp(key, "timeout_ms")) c->timeout_ms = value;
+    else return fail("dlnb_comm_set: unknown key %s", key);
+    return 0;
+}
+extern "C" long dlnb_comm_get(dlnb_comm_t c, const char *key) {
+    if (!c) return -1;
+    if (!strcmp(key, "ctas")) return c->ctas;
+    if (!strcmp(key, "threads")) return c->threads;
+    if (!strcmp(key, "algo")) return c->algo;
+    if (!strcmp(key, "twoshot_min_bytes")) return c->twoshot_min_bytes;
+    if (!strcmp(key, "timeout_ms")) return c->timeout_ms;
+    if (!strcmp(key, "id")) return c->id;
+    return -1;
+}
+
+// ---------------------------------------------------------------------------
+// emulated compute
+// ---------------------------------------------------------------------------
+extern "C" int dlnb_compute_spin(double usec) {
+    NEED_INIT();
+    if (!(usec > 0)) return 0;
+    double req = (usec - G.spin_overhead_us) / G.spin_slope;
+    if (req < 0) req = 0;
+    spin_kernel<<<(unsigned)G.spin_ctas, (unsigned)G.spin_threads, 0, G.s_compute>>>(
+        (unsigned long long)(req * 1000.0 + 0.5));
+    CU_TRY(cudaGetLastError());
+    G.launches++;
+    G.compute_dirty = true;
+    return 0;
+}
+extern "C" int dlnb_compute_sync(void) {
+    NEED_INIT();
+    CU_TRY(cudaStreamSynchronize(G.s_compute));
+    return 0;
+}
+extern "C" int dlnb_spin_calibrate(double *overhead_us, double *slope) {
+    NEED_INIT();
+    // K back-to-back spins of `req` us each between two events: per-spin cost
+    // includes the kernel-to-kernel gap, which is what the proxies see.
+    const double reqs[3] = {20.0, 200.0, 1000.0};
+    double got[3];
+    const int K = 16;
+    CU_TRY(cudaStreamSynchronize(G.s_compute));
+    for (int i = 0; i < 3; ++i) {
+        double best = 1e30;
+        for (int rep = 0; rep < 3; ++rep) {
+            CU_TRY(cudaEventRecord(G.ev_tmp0, G.s_compute));
+            for (int k = 0; k < K; ++k) {
+                spin_kernel<<<(unsigned)G.spin_ctas, (unsigned)G.spin_threads, 0, G.s_compute>>>(
+                    (unsigned long long)(reqs[i] * 1000.0));
+                G.launches++;
+            }
+            CU_TRY(cudaEventRecord(G.ev_tmp1, G.s_compute));
+            CU_TRY(cudaEventSynchronize(G.ev_tmp1));
+            float ms = 0;
+            CU_TRY(cudaEventElapsedTime(&ms, G.ev_tmp0, G.ev_tmp1));
+            best = std::min(best, (double)ms * 1000.0 / K);
+        }
+        got[i] = best;
+    }
+    // least squares through the three points
+    double sx = 0, sy = 0, sxx = 0, sxy = 0;
+    for (int i = 0; i < 3; ++i) { sx += reqs[i]; sy += got[i]; sxx += reqs[i] * reqs[i]; sxy += reqs[i] * got[i]; }
+    double b = (3 * sxy - sx * sy) / (3 * sxx - sx * sx);
+    double a = (sy - b * sx) / 3;
+    if (!(b > 0.5 && b < 2.0)) { a = 0; b = 1; }
+    if (a < 0) a = 0;
+    G.spin_overhead_us = a;
+    G.spin_slope = b;
+    if (overhead_us) *overhead_us = a;
+    if (slope) *slope = b;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// collective launch
+// ---------------------------------------------------------------------------
+static cudaError_t launch_dtype(int dtype, int op, int nr, dim3 grid, int threads, cudaStream_t s,
+                                const EmuViews &ev, size_t count, bool coop) {
+    switch (dtype) {
+    case DLNB_F32: return launch_coll_f32(op, nr, grid, threads, s, ev, count, coop);
+    case DLNB_F16: return launch_coll_f16(op, nr, grid, threads, s, ev, count, coop);
+    case DLNB_BF16: return launch_coll_bf16(op, nr, grid, threads, s, ev, count, coop);
+    }
+    return cudaErrorInvalidValue;
+}
+static int occupancy_dtype(int dtype, int op, int nr, int threads) {
+    switch (dtype) {
+    case DLNB_F32: return occupancy_coll_f32(op, nr, threads);
+    case DLNB_F16: return occupancy_coll_f16(op, nr, threads);
+    case DLNB_BF16: return occupancy_coll_bf16(op, nr, threads);
+    }
+    return 0;
+}
+
+// bytes the kernel's vector loop walks on this rank (sizes the grid)
+static size_t work_bytes(int op, int n, size_t count, size_t esz) {
+    switch (op) {
+    case OP_AR1: return count * esz;
+    case OP_AR2: return count * esz / (size_t)n;
+    case OP_AG: return count * esz;
+    default: return count * esz;
+    }
+}
+
+static int pick_grid(long want, int dtype, int op, int n, int threads, size_t bytes, int *out) {
+    int occ = occupancy_dtype(dtype, op, n, threads);
+    if (occ <= 0) return fail("collective kernel does not fit on an SM with %d threads", threads);
+    int cap = std::min(G.sms * occ, MAX_FLAG_CTAS);
+    long g;
+    if (want > 0) {
+        g = want;
+    } else if (n == 1) {
+        g = (long)G.sms * occ; // pure HBM copy: fill the machine
+    } else {
+        g = 64; // NVLink-bound: enough bytes in flight without taking every SM
+    }
+    // no more CTAs than 16-byte vectors / threads
+    const size_t vecs = bytes / 16 + 1;
+    const long useful = (long)((vecs + threads - 1) / threads);
+    g = std::min(g, std::max(1L, useful));
+    g = std::min<long>(g, cap);
+    *out = (int)std::max(1L, g);
+    return 0;
+}
+
+static int join_streams() {
+    // the collective may not start before compute / copies enqueued so far
+    if (G.compute_dirty) {
+        CU_TRY(cudaEventRecord(G.ev_join, G.s_compute));
+        CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_join, 0));
+        G.compute_dirty = false;
+    }
+    if (G.copy_dirty) {
+        CU_TRY(cudaEventRecord(G.ev_copy, G.s_copy));
+        CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_copy, 0));
+        G.copy_dirty = false;
+    }
+    return 0;
+}
+
+static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count, int slot) {
+    NEED_INIT();
+    if (!c) return fail("null communicator");
+    if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range (communicator has %d)", slot, c->num_slots);
+    if (count && (!send || !recv)) return fail("null buffer");
+    const size_t esz = dtype_size(c->dtype);
+    if (op == OP_AR1 || op == OP_AR2) {
+        const size_t bytes = count * esz;
+        const bool small = (size_t)c->twoshot_min_bytes > bytes;
+        if (c->algo == DLNB_ALGO_ONESHOT) op = OP_AR1;
+        else if (c->algo == DLNB_ALGO_TWOSHOT) op = OP_AR2;
+        else op = (c->n == 1 || small) ? OP_AR1 : OP_AR2;
+    }
+    if (join_streams()) return 1;
+    if (G.slot_timing) CU_TRY(cudaEventRecord(c->ev_start[slot], G.s_comm));
+    if (count) {
+        EmuViews ev;
+        RankView &v = ev.v[0];
+        memset(&v, 0, sizeof(v));
+        v.rank = c->me;
+        v.nranks = c->n;
+        for (int i = 0; i < c->n; ++i) {
+            char *s = translate(send, c->ranks[i]);
+            char *r = translate(recv, c->ranks[i]);
+            if (!s || !r) return fail("buffer %p/%p is not in the symmetric arena (use dlnb_symm_alloc)", send, recv);
+            v.send[i] = s;
+            v.recv[i] = r;
+            v.flags[i] = (uint32_t *)translate(G.flag_area + (size_t)c->id * FLAG_BYTES_PER_COMM, c->ranks[i]);
+        }
+        v.ctl = G.ctl + c->id;
+        v.host_error = G.host_error_dev;
+        v.timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;
+        int grid = 1;
+        const int threads = (int)c->threads;
+        if (pick_grid(c->ctas, c->dtype, op, c->n, threads, work_bytes(op, c->n, count, esz), &grid)) return 1;
+        cudaError_t e = launch_dtype(c->dtype, op, c->n, dim3(grid, 1, 1), threads, G.s_comm, ev, count, false);
+        if (e != cudaSuccess) return fail("collective launch failed: %s", cudaGetErrorString(e));
+        G.launches++;
+    }
+    CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+    c->slot_used[slot] = 1;
+    return 0;
+}
+
+static int check_watchdog() {
+    if (G.host_error && *(volatile uint32_t *)G.host_error)
+        return fail("cross-GPU flag barrier timed out: a peer rank is dead or out of order");
+    return 0;
+}
+
+extern "C" int dlnb_iallreduce(dlnb_comm_t c, const void *send, void *recv, size_t count, int slot) {
+    return coll(c, OP_AR2, send, recv, count, slot);
+}
+extern "C" int dlnb_iallgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount, int slot) {
+    return coll(c, OP_AG, send, recv, sendcount, slot);
+}
+extern "C" int dlnb_ireduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount, int slot) {
+    return coll(c, OP_RS, send, recv, recvcount, slot);
+}
+extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
+    NEED_INIT();
+    if (!c) return fail("null communicator");
+    if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
+    if (!c->slot_used[slot]) return 0;
+    CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
+    return check_watchdog();
+}
+extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
+    NEED_INIT();
+    if (!c) return fail("null communicator");
+    if (nslots > c->num_slots) nslots = c->num_slots;
+    // the communication stream is ordered: waiting for the newest used slot suffices,
+    // but slots may have been recorded in any order, so wait for each.
+    for (int i = 0; i < nslots; ++i)
+        if (c->slot_used[i]) CU_TRY(cudaEventSynchronize(c->ev_end[i]));
+    return check_watchdog();
+}
+extern "C" int dlnb_barrier(dlnb_comm_t c) {
+    NEED_INIT();
+    if (!c) return fail("null communicator");
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    return check_watchdog();
+}
+extern "C" int dlnb_allreduce(dlnb_comm_t c, const void *send, void *recv, size_t count) {
+    if (coll(c, OP_AR2, send, recv, count, 0)) return 1;
+    return dlnb_wait(c, 0);
+}
+extern "C" int dlnb_allgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount) {
+    if (coll(c, OP_AG, send, recv, sendcount, 0)) return 1;
+    return dlnb_wait(c, 0);
+}
+extern "C" int dlnb_reduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount) {
+    if (coll(c, OP_RS, send, recv, recvcount, 0)) return 1;
+    return dlnb_wait(c, 0);
+}
+extern "C" int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms) {
+    NEED_INIT();
+    if (!c || !ms) return fail("null argument");
+    if (slot < 0 || slot >= c->num_slots || !c->slot_used[slot]) return fail("slot %d has no recorded collective", slot);
+    CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
+    CU_TRY(cudaEventElapsedTime(ms, c->ev_start[slot], c->ev_end[slot]));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// device timing of one proxy iteration (both streams)
+// ---------------------------------------------------------------------------
+extern "C" int dlnb_iter_begin(void) {
+    NEED_INIT();
+    // the iteration starts when both streams are idle up to here
+    CU_TRY(cudaEventRecord(G.ev_join, G.s_comm));
+    CU_TRY(cudaStreamWaitEvent(G.s_compute, G.ev_join, 0));
+    CU_TRY(cudaEventRecord(G.ev_iter0, G.s_compute));
+    CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_iter0, 0));
+    CU_TRY(cudaStreamWaitEvent(G.s_copy, G.ev_iter0, 0));
+    return 0;
+}
+extern "C" int dlnb_iter_end(float *ms) {
+    NEED_INIT();
+    G.compute_dirty = true;
+    G.copy_dirty = true;
+    if (join_streams()) return 1;
+    CU_TRY(cudaEventRecord(G.ev_iter1, G.s_comm));
+    CU_TRY(cudaEventSynchronize(G.ev_iter1));
+    if (ms) CU_TRY(cudaEventElapsedTime(ms, G.ev_iter0, G.ev_iter1));
+    return check_watchdog();
+}
+
+// ---------------------------------------------------------------------------
+// buffer helpers
+// ---------------------------------------------------------------------------
+extern "C" int dlnb_memcpy_h2d(void *dst, const void *src, size_t bytes) {
+    NEED_INIT();
+    CU_TRY(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+extern "C" int dlnb_memcpy_d2h(void *dst, const void *src, size_t bytes) {
+    NEED_INIT();
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    CU_TRY(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+extern "C" int dlnb_memcpy_h2d_async(void *dst, const void *src, size_t bytes) {
+    NEED_INIT();
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, G.s_copy));
+    G.copy_dirty = true;
+    return 0;
+}
+extern "C" int dlnb_memcpy_d2h_async(void *dst, const void *src, size_t bytes) {
+    NEED_INIT();
+    // results are produced on the communication stream
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, G.s_comm));
+    return 0;
+}
+extern "C" int dlnb_host_alloc(size_t bytes, void **ptr) {
+    NEED_INIT();
+    CU_TRY(cudaHostAlloc(ptr, bytes, cudaHostAllocDefault));
+    return 0;
+}
+extern "C" int dlnb_host_free(void *ptr) {
+    if (ptr) cudaFreeHost(ptr);
+    return 0;
+}
+
+static int aux_grid(size_t n) {
+    size_t g = (n + 255) / 256;
+    return (int)std::max<size_t>(1, std::min<size_t>(g, (size_t)G.sms * 8));
+}
+
+extern "C" int dlnb_fill_pattern(void *ptr, size_t count, int dtype, int kind, uint64_t seed, int as_rank) {
+    NEED_INIT();
+    if (!count) return 0;
+    const int g = aux_grid(count);
+    if (dtype == DLNB_F32) fill_kernel<float><<<g, 256, 0, G.s_comm>>>((float *)ptr, count, kind, seed, as_rank);
+    else if (dtype == DLNB_F16) fill_kernel<__half><<<g, 256, 0, G.s_comm>>>((__half *)ptr, count, kind, seed, as_rank);
+    else if (dtype == DLNB_BF16)
+        fill_kernel<__nv_bfloat16><<<g, 256, 0, G.s_comm>>>((__nv_bfloat16 *)ptr, count, kind, seed, as_rank);
+    else return fail("unknown dtype %d", dtype);
+    CU_TRY(cudaGetLastError());
+    G.launches++;
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    return 0;
+}
+
+extern "C" int dlnb_verify_sum_pattern(const void *ptr, size_t count, size_t elem_offset, int dtype, int kind,
+                                       uint64_t seed, const int *ranks, int nranks, uint64_t *mismatches) {
+    NEED_INIT();
+    if (!mismatches || !ranks || nranks < 1 || nranks > MAXR) return fail("bad argument");
+    RankList rl;
+    rl.n = nranks;
+    for (int i = 0; i < nranks; ++i) rl.r[i] = ranks[i];
+    CU_TRY(cudaMemsetAsync(G.d_scalar, 0, sizeof(unsigned long long), G.s_comm));
+    if (count) {
+        const int g = aux_grid(count);
+        if (dtype == DLNB_F32)
+            verify_sum_kernel<float><<<g, 256, 0, G.s_comm>>>((const float *)ptr, count, elem_offset, kind, seed, rl, G.d_scalar);
+        else if (dtype == DLNB_F16)
+            verify_sum_kernel<__half><<<g, 256, 0, G.s_comm>>>((const __half *)ptr, count, elem_offset, kind, seed, rl, G.d_scalar);
+        else if (dtype == DLNB_BF16)
+            verify_sum_kernel<__nv_bfloat16><<<g, 256, 0, G.s_comm>>>((const __nv_bfloat16 *)ptr, count, elem_offset, kind, seed, rl, G.d_scalar);
+        else return fail("unknown dtype %d", dtype);
+        CU_TRY(cudaGetLastError());
+        G.launches++;
+    }
+    unsigned long long h = 0;
+    CU_TRY(cudaMemcpyAsync(&h, G.d_scalar, sizeof(h), cudaMemcpyDeviceToHost, G.s_comm));
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    *mismatches = h;
+    return 0;
+}
+
+extern "C" int dlnb_checksum(const void *ptr, size_t bytes, uint64_t *out) {
+    NEED_INIT();
+    if (!out) return fail("null out pointer");
+    CU_TRY(cudaMemsetAsync(G.d_scalar, 0, sizeof(unsigned long long), G.s_comm));
+    const size_t nwords = bytes / 4;
+    if (nwords) {
+        checksum_kernel<<<aux_grid(nwords), 256, 0, G.s_comm>>>((const uint32_t *)ptr, nwords, G.d_scalar);
+        CU_TRY(cudaGetLastError());
+        G.launches++;
+    }
+    unsigned long long h = 0;
+    CU_TRY(cudaMemcpyAsync(&h, G.d_scalar, sizeof(h), cudaMemcpyDeviceToHost, G.s_comm));
+    uint32_t tail = 0;
+    if (bytes % 4) CU_TRY(cudaMemcpyAsync(&tail, (const char *)ptr + nwords * 4, bytes % 4, cudaMemcpyDeviceToHost, G.s_comm));
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    *out = h + (uint64_t)mix32(tail + (uint32_t)nwords * 0x9e3779b9u) * (bytes % 4 ? 1 : 0);
+    return 0;
+}
+
+extern "C" int dlnb_flush_l2(void) {
+    NEED_INIT();
+    if (!G.flush_buf) {
+        G.flush_bytes = 256u << 20; // 2x the 126 MB L2
+        CU_TRY(cudaMalloc(&G.flush_buf, G.flush_bytes));
+    }
+    static uint32_t tag = 0;
+    flush_kernel<<<G.sms * 4, 512, 0, G.s_comm>>>((uint4 *)G.flush_buf, G.flush_bytes / 16, ++tag);
+    CU_TRY(cudaGetLastError());
+    G.launches++;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// single-GPU emulation of an n-rank collective (test vehicle)
+// ---------------------------------------------------------------------------
+static int emu(int op, int nranks, const void *const *send, void *const *recv, size_t count, int dtype, int ctas) {
+    NEED_INIT();
+    if (nranks < 1 || nranks > MAXR) return fail("emu: nranks %d not in 1..%d", nranks, MAXR);
+    if (!send || !recv) return fail("emu: null buffer list");
+    if (!count) return 0;
+    if (!G.emu_flags) {
+        CU_TRY(cudaMalloc((void **)&G.emu_flags, MAXR * FLAG_BYTES_PER_COMM));
+        CU_TRY(cudaMemset(G.emu_flags, 0, MAXR * FLAG_BYTES_PER_COMM));
+        CU_TRY(cudaMalloc((void **)&G.emu_ctl, MAXR * sizeof(CommCtl)));
+        CU_TRY(cudaMemset(G.emu_ctl, 0, MAXR * sizeof(CommCtl)));
+    }
+    EmuViews ev;
+    memset(&ev, 0, sizeof(ev));
+    for (int r = 0; r < nranks; ++r) {
+        RankView &v = ev.v[r];
+        v.rank = r;
+        v.nranks = nranks;
+        for (int p = 0; p < nranks; ++p) {
+            v.send[p] = send[p];
+            v.recv[p] = recv[p];
+            v.flags[p] = (uint32_t *)((char *)G.emu_flags + (size_t)p * FLAG_BYTES_PER_COMM);
+        }
+        v.ctl = G.emu_ctl + r;
+        v.host_error = G.host_error_dev;
+        v.timeout_ns = 10ull * 1000000000ull;
+    }
+    const int threads = 512;
+    int occ = occupancy_dtype(dtype, op, nranks, threads);
+    if (occ <= 0) return fail("emu: kernel does not fit");
+    // all virtual ranks' CTAs must be co-resident: they wait on one another
+    int cap = std::min((G.sms * occ) / nranks, MAX_FLAG_CTAS);
+    int grid = ctas > 0 ? std::min(ctas, cap) : std::min(16, cap);
+    if (grid < 1) return fail("emu: device too small for %d virtual ranks", nranks);
+    cudaError_t e = launch_dtype(dtype, op, nranks, dim3(grid, nranks, 1), threads, G.s_comm, ev, count, true);
+    if (e != cudaSuccess) return fail("emu launch failed: %s", cudaGetErrorString(e));
+    G.launches++;
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    return check_watchdog();
+}
+
+extern "C" int dlnb_emu_allreduce(int nranks, const void *const *send, void *const *recv, size_t count, int dtype,
+                                  int algo, int ctas) {
+    int op = (algo == DLNB_ALGO_ONESHOT) ? OP_AR1 : (algo == DLNB_ALGO_TWOSHOT) ? OP_AR2
+             : (count * dtype_size(dtype) < 256 * 1024 ? OP_AR1 : OP_AR2);
+    return emu(op, nranks, send, recv, count, dtype, ctas);
+}
+extern "C" int dlnb_emu_allgather(int nranks, const void *const *send, void *const *recv, size_t sendcount, int dtype,
+                                  int ctas) {
+    return emu(OP_AG, nranks, send, recv, sendcount, dtype, ctas);
+}
+extern "C" int dlnb_emu_reduce_scatter(int nranks, const void *const *send, void *const *recv, size_t recvcount,
+                                       int dtype, int ctas) {
+    return emu(OP_RS, nranks, send, recv, recvcount, dtype, ctas);
+}

@@ -1,0 +1,174 @@
+/*
+ * dlnb.h — C ABI of the B200-native data-parallel hot path of DLNetBench.
+ *
+ * This is the drop-in boundary: plain C, plain pointers and sizes. The C++ host
+ * side (cpp/proxy_classes.hpp: class B200Communicator : ProxyCommunicator) and
+ * the Python test/bench harness (dlnetbench_b200/capi.py, ctypes) both bind
+ * exactly these symbols from libdlnb.so.
+ *
+ * Each entry point cites the reference interface it replaces
+ * (paths relative to the reference tree, HicrestLaboratory/DLNetBench).
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on error; the message is
+ *     available from dlnb_last_error() (the C++ wrapper prints "[rank r] msg"
+ *     and exits, like the reference's CCUTILS_GPU_CHECK / MPI_ERRORS_ARE_FATAL).
+ *   - one process per GPU, one host thread; not re-entrant.
+ *   - `count` arguments are in ELEMENTS of the communicator's dtype and are
+ *     size_t here (the reference's `int count` is widened by the C++ wrapper,
+ *     which rejects negative values).
+ *   - all data buffers passed to collectives must come from dlnb_symm_alloc()
+ *     (the symmetric arena): kernels address the peers' copies of the same
+ *     allocation directly over NVLink.
+ *   - ranks of a communicator must issue collectives in the same order.
+ */
+#ifndef DLNB_H
+#define DLNB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLNB_MAX_RANKS 8
+
+typedef struct dlnb_comm *dlnb_comm_t;
+
+/* element types; reference: cpp/data_types.hpp:36-51 (_FLOAT / NCCL_FLOAT_TYPE) */
+enum dlnb_dtype { DLNB_F32 = 0, DLNB_F16 = 1, DLNB_BF16 = 2 };
+
+/* collective algorithm selector (DLNB_ALGO_AUTO picks by message size) */
+enum dlnb_algo { DLNB_ALGO_AUTO = 0, DLNB_ALGO_ONESHOT = 1, DLNB_ALGO_TWOSHOT = 2 };
+
+/* buffer fill patterns used by tests/bench (SURVEY §8c pins) */
+enum dlnb_pattern { DLNB_PAT_ZERO = 0, DLNB_PAT_INT = 1, DLNB_PAT_UNIFORM = 2 };
+
+/* ---- process / device set-up ------------------------------------------------
+ * Replaces MPI_Init + set_local_device + ncclGetUniqueId/MPI_Bcast/ncclCommInitRank
+ * (cpp/data_parallel/dp.cpp:166-189, cpp/utils.hpp:74-117).
+ * `session` names the rendezvous (abstract unix socket) shared by the `world`
+ * processes of one box; rank 0 is the hub. world==1 needs no rendezvous. */
+int dlnb_init(int rank, int world, int device, const char *session);
+/* Replaces MPI_Finalize / CCLCommunicator::finalize (proxy_classes.hpp:229-234). */
+int dlnb_finalize(void);
+int dlnb_rank(void);
+int dlnb_world(void);
+int dlnb_device(void);
+const char *dlnb_last_error(void);
+const char *dlnb_version(void);
+/* "vmm" (cuMem + POSIX fd export) or "ipc" (cudaIpc, diagnostic only) or "local" (world==1) */
+const char *dlnb_arena_kind(void);
+
+/* ---- host-side rendezvous helpers -------------------------------------------
+ * Replace the MPI calls the mains make outside the hot path: MPI_Barrier
+ * (dp.cpp:234), MPI_Allgather of strings (netcommunicators.hpp:19-77),
+ * MPI_Allreduce/MPI_Bcast in estimate_runs (utils.hpp:127-132). */
+int dlnb_host_barrier(void);
+int dlnb_host_allgather(const void *in, size_t bytes, void *out);
+
+/* ---- symmetric arena ---------------------------------------------------------
+ * Replaces Tensor<T,Device::GPU>'s cudaMalloc + cudaMemset(0)
+ * (cpp/proxy_classes.hpp:401-405). Collective: every rank calls it in the same
+ * order with the same size. Memory is zero-filled. */
+int dlnb_symm_alloc(size_t bytes, void **ptr);
+/* Replaces CCUTILS_CUDA_FREE_SAFE (proxy_classes.hpp:434). The arena is a bump
+ * allocator; memory is returned at dlnb_finalize(). */
+int dlnb_symm_free(void *ptr);
+size_t dlnb_symm_bytes_in_use(void);
+
+/* ---- communicators -----------------------------------------------------------
+ * Replaces `new CCLCommunicator(comm, num_streams)` / `new MPICommunicator(comm,
+ * MPI_FLOAT, num_requests)` and MPI_Comm_split / ncclCommSplit
+ * (proxy_classes.hpp:55-64,138-147; fsdp.cpp:258-283). `ranks` lists the world
+ * ranks of the group in group order; must contain the caller. Collective over the
+ * WORLD (every world rank creates its communicators in the same order). */
+int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int dtype, dlnb_comm_t *out);
+int dlnb_comm_destroy(dlnb_comm_t c);
+int dlnb_comm_rank(dlnb_comm_t c);
+int dlnb_comm_size(dlnb_comm_t c);
+/* tuning knobs: "ctas" (CTAs per collective kernel), "threads", "algo" (dlnb_algo),
+ * "twoshot_min_bytes" (AUTO threshold), "timeout_ms" (flag-spin watchdog). */
+int dlnb_comm_set(dlnb_comm_t c, const char *key, long value);
+long dlnb_comm_get(dlnb_comm_t c, const char *key);
+
+/* ---- emulated compute --------------------------------------------------------
+ * Replaces usleep(fwd) / usleep(bwd) (dp.cpp:93,98; fsdp.cpp:103,120,145) with a
+ * calibrated %globaltimer spin kernel on the compute stream. Asynchronous. */
+int dlnb_compute_spin(double usec);
+int dlnb_compute_sync(void);
+/* Measures requested→achieved duration of the spin kernel and stores the linear
+ * correction; returns fixed overhead (us) and slope through the out-params. */
+int dlnb_spin_calibrate(double *overhead_us, double *slope);
+/* "spin_ctas": CTAs of the spin kernel (SM footprint of the emulated compute). */
+int dlnb_set(const char *key, long value);
+long dlnb_get(const char *key);
+
+/* ---- collectives (asynchronous; ordered on the communication stream) ----------
+ * Each first waits (device-side event) for the compute enqueued so far, so a
+ * collective cannot start before "its" backward finished — this replaces the host
+ * ordering usleep → Iallreduce of the reference. `slot` is the reference's
+ * `index` (request / stream id). */
+/* ProxyCommunicator::Iallreduce (proxy_classes.hpp:32,66-68,149-152) */
+int dlnb_iallreduce(dlnb_comm_t c, const void *send, void *recv, size_t count, int slot);
+/* ProxyCommunicator::Iallgather (proxy_classes.hpp:34-35,91-93,202-204); recvcount==sendcount */
+int dlnb_iallgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount, int slot);
+/* non-blocking form of Reduce_Scatter_block, same semantics as below */
+int dlnb_ireduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount, int slot);
+/* ProxyCommunicator::Allreduce (proxy_classes.hpp:33,70-72,154-158): blocking */
+int dlnb_allreduce(dlnb_comm_t c, const void *send, void *recv, size_t count);
+/* ProxyCommunicator::Allgather (proxy_classes.hpp:36-37,95-97,197-200): blocking */
+int dlnb_allgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount);
+/* ProxyCommunicator::Reduce_Scatter_block (proxy_classes.hpp:38,99-101,206-209): blocking */
+int dlnb_reduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount);
+/* ProxyCommunicator::Wait / WaitAll / Barrier (proxy_classes.hpp:41-43,79-89,184-195) */
+int dlnb_wait(dlnb_comm_t c, int slot);
+int dlnb_waitall(dlnb_comm_t c, int nslots);
+int dlnb_barrier(dlnb_comm_t c);
+/* number of kernels this library has launched so far (bench "gpu_launches") */
+uint64_t dlnb_launch_count(void);
+
+/* ---- device timing -------------------------------------------------------------
+ * Added (no reference counterpart; the reference only has host timers,
+ * ccutils CCUTILS_MPI_TIMER_*): cudaEvent pair spanning both streams. */
+int dlnb_iter_begin(void);
+int dlnb_iter_end(float *ms);
+/* device time of the most recent collective recorded in `slot` (ms) */
+int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms);
+
+/* ---- buffer helpers (tests, bench, end-to-end path) ----------------------------- */
+int dlnb_memcpy_h2d(void *dst, const void *src, size_t bytes);
+int dlnb_memcpy_d2h(void *dst, const void *src, size_t bytes);
+/* asynchronous copies on the communication stream from/to pinned host memory */
+int dlnb_memcpy_h2d_async(void *dst, const void *src, size_t bytes);
+int dlnb_memcpy_d2h_async(void *dst, const void *src, size_t bytes);
+int dlnb_host_alloc(size_t bytes, void **ptr);
+int dlnb_host_free(void *ptr);
+/* x[i] = pattern(kind, seed, as_rank, i), i in [0,count) */
+int dlnb_fill_pattern(void *ptr, size_t count, int dtype, int kind, uint64_t seed, int as_rank);
+/* counts elements of `ptr` that differ (bitwise) from the rank-order fp32 sum over
+ * `ranks` of pattern(kind, seed, r, elem_offset + i), rounded once to dtype. */
+int dlnb_verify_sum_pattern(const void *ptr, size_t count, size_t elem_offset, int dtype, int kind,
+                            uint64_t seed, const int *ranks, int nranks, uint64_t *mismatches);
+/* order-independent 64-bit checksum of a device buffer (sum of mixed 32-bit words) */
+int dlnb_checksum(const void *ptr, size_t bytes, uint64_t *out);
+/* writes a buffer larger than L2 (timing hygiene between timed iterations) */
+int dlnb_flush_l2(void);
+
+/* ---- single-GPU emulation of an n-rank collective --------------------------------
+ * Test vehicle (no reference counterpart): runs the SAME device code as the
+ * multi-GPU path for `nranks` virtual ranks inside one cooperative kernel launch on
+ * one GPU (gridDim.y = virtual rank), including the flag barriers. send[r]/recv[r]
+ * are ordinary device pointers (dlnb_symm_alloc or cudaMalloc). */
+int dlnb_emu_allreduce(int nranks, const void *const *send, void *const *recv, size_t count,
+                       int dtype, int algo, int ctas);
+int dlnb_emu_allgather(int nranks, const void *const *send, void *const *recv, size_t sendcount,
+                       int dtype, int ctas);
+int dlnb_emu_reduce_scatter(int nranks, const void *const *send, void *const *recv,
+                            size_t recvcount, int dtype, int ctas);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLNB_H */

@@ -1,0 +1,192 @@
+"""Parity tests proper: the CUDA path (through the C ABI) against the CPU oracle.
+
+Multi-rank cases run the SAME device code as the multi-GPU path for n virtual ranks
+inside one cooperative launch on one GPU (dlnb_emu_*), flag barriers included.
+Bar: bit-exact — the kernels and the oracle both accumulate in fp32 in rank order
+0..n-1 and round once, so even random data must match bit for bit; the stated
+north-star tolerance (2*(n-1)*eps relative) is therefore met with zero error.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+NPDT = {0: np.float32, 1: np.float16, 2: np.uint16}
+EDGE_COUNTS = [1, 7, 8, 15, 33, 4095, 4097, 65536 + 17, 1_000_003]
+
+
+def host_inputs(oracle, n, count, dtype, kind, seed=1234):
+    return [oracle.fill_pattern(count, dtype, kind, seed, r) for r in range(n)]
+
+
+def bits(a):
+    return a.view(np.uint32) if a.dtype == np.float32 else a.view(np.uint16)
+
+
+def make_dev(dl, arrays, dtype):
+    ts = []
+    for a in arrays:
+        t = dl.Tensor(a.size, dtype)
+        t.upload(a)
+        ts.append(t)
+    return ts
+
+
+@pytest.mark.parametrize("dtype", [0, 1, 2])
+@pytest.mark.parametrize("count", EDGE_COUNTS)
+def test_world1_allreduce_is_bit_copy(dl, oracle, dtype, count):
+    comm = dl.B200Communicator([0], num_slots=2, dtype=dtype)
+    x = host_inputs(oracle, 1, count, dtype, 2)[0]
+    send, = make_dev(dl, [x], dtype)
+    recv = dl.Tensor(count, dtype)
+    comm.Iallreduce(send.data, recv.data, count, 1)
+    comm.WaitAll(2)
+    got = recv.download(NPDT[dtype])
+    want = oracle.allreduce([x], dtype)
+    assert np.array_equal(bits(got), bits(want))
+    comm.finalize()
+
+
+@pytest.mark.parametrize("algo", [1, 2])
+@pytest.mark.parametrize("dtype", [0, 1, 2])
+@pytest.mark.parametrize("n", [2, 3, 4, 8])
+def test_emu_allreduce_matches_oracle(dl, oracle, n, dtype, algo):
+    for kind in (1, 2):
+        for count in EDGE_COUNTS:
+            xs = host_inputs(oracle, n, count, dtype, kind)
+            send = make_dev(dl, xs, dtype)
+            recv = [dl.Tensor(count, dtype) for _ in range(n)]
+            dl.emu_allreduce([t.data for t in send], [t.data for t in recv], count, dtype, algo=algo, ctas=4)
+            want = oracle.allreduce(xs, dtype)
+            for r in range(n):
+                got = recv[r].download(NPDT[dtype])
+                assert np.array_equal(bits(got), bits(want)), (n, dtype, algo, kind, count, r)
+            # inputs untouched
+            assert np.array_equal(bits(send[0].download(NPDT[dtype])), bits(xs[0]))
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_emu_allgather_matches_oracle(dl, oracle, n, dtype):
+    for count in EDGE_COUNTS:  # odd counts exercise the misaligned-destination path
+        xs = host_inputs(oracle, n, count, dtype, 2)
+        send = make_dev(dl, xs, dtype)
+        recv = [dl.Tensor(count * n, dtype) for _ in range(n)]
+        dl.emu_allgather([t.data for t in send], [t.data for t in recv], count, dtype, ctas=4)
+        want = oracle.allgather(xs, dtype)
+        for r in range(n):
+            assert np.array_equal(bits(recv[r].download(NPDT[dtype])), bits(want)), (n, dtype, count, r)
+
+
+@pytest.mark.parametrize("dtype", [0, 1, 2])
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_emu_reduce_scatter_matches_oracle(dl, oracle, n, dtype):
+    for kind in (1, 2):
+        for count in EDGE_COUNTS:
+            xs = host_inputs(oracle, n, count * n, dtype, kind)
+            send = make_dev(dl, xs, dtype)
+            recv = [dl.Tensor(count, dtype) for _ in range(n)]
+            dl.emu_reduce_scatter([t.data for t in send], [t.data for t in recv], count, dtype, ctas=4)
+            for r in range(n):
+                want = oracle.reduce_scatter_block(xs, r, count, dtype)
+                assert np.array_equal(bits(recv[r].download(NPDT[dtype])), bits(want)), (n, dtype, kind, count, r)
+
+
+def test_emu_allreduce_many_ctas_and_repeats(dl, oracle):
+    """Flag generations stay consistent across back-to-back launches with different grids."""
+    n, dtype, count = 8, 1, 3_000_001
+    xs = host_inputs(oracle, n, count, dtype, 2)
+    send = make_dev(dl, xs, dtype)
+    recv = [dl.Tensor(count, dtype) for _ in range(n)]
+    want = oracle.allreduce(xs, dtype)
+    for ctas in (1, 16, 2, 9, 18):
+        for algo in (1, 2):
+            for t in recv:
+                t.fill(0)
+            dl.emu_allreduce([t.data for t in send], [t.data for t in recv], count, dtype, algo=algo, ctas=ctas)
+            for r in (0, n - 1):
+                assert np.array_equal(bits(recv[r].download(NPDT[dtype])), bits(want)), (ctas, algo, r)
+
+
+def test_integer_pattern_is_exact_in_any_order(dl, oracle):
+    """SURVEY §8c pin (1): |x|<=8 so sums are exact in fp16 — closed form on device."""
+    n, dtype, count = 8, 1, 2_000_003
+    send = [dl.Tensor(count, dtype) for _ in range(n)]
+    recv = [dl.Tensor(count, dtype) for _ in range(n)]
+    for r, t in enumerate(send):
+        t.fill(1, 0, r)
+    dl.emu_allreduce([t.data for t in send], [t.data for t in recv], count, dtype, algo=2, ctas=8)
+    for r in range(n):
+        assert dl.verify_sum_pattern(recv[r].data, count, 0, dtype, 1, 0, list(range(n))) == 0
+    # and the device-side generator agrees with the oracle's
+    assert np.array_equal(bits(send[3].download(np.float16)), bits(oracle.fill_pattern(count, dtype, 1, 0, 3)))
+
+
+@pytest.mark.parametrize("dtype,count", [(1, 803_026_125), (0, 77_403_008)])
+def test_full_size_bucket_world1(dl, oracle, dtype, count):
+    """BASELINE sizes: one llama3_8b fp16 bucket (N=10, odd count) and one gpt2_l fp32 bucket.
+    Too big for the CPU oracle in seconds -> size-independent properties: closed-form
+    verification on device and checksum(send) == checksum(recv)."""
+    comm = dl.B200Communicator([0], num_slots=1, dtype=dtype)
+    send, recv = dl.Tensor(count, dtype), dl.Tensor(count, dtype)
+    send.fill(2, 99, 0)
+    comm.Iallreduce(send.data, recv.data, count, 0)
+    comm.WaitAll(1)
+    assert dl.verify_sum_pattern(recv.data, count, 0, dtype, 2, 99, [0]) == 0
+    assert send.checksum() == recv.checksum()
+    # checksum kernel agrees with the oracle's on a prefix
+    pre = 1 << 20
+    assert oracle.checksum(recv.download(NPDT[dtype], pre)) == recv.checksum(pre * (4 if dtype == 0 else 2))
+    comm.finalize()
+
+
+def test_world1_allgather_and_reduce_scatter(dl, oracle):
+    dtype, count = 1, 31_368_208 // 16 + 3
+    comm = dl.B200Communicator([0], num_slots=4, dtype=dtype)
+    x = host_inputs(oracle, 1, count, dtype, 2)[0]
+    send, = make_dev(dl, [x], dtype)
+    gathered, shard = dl.Tensor(count, dtype), dl.Tensor(count, dtype)
+    comm.Allgather(send.data, count, gathered.data, count)
+    assert np.array_equal(bits(gathered.download(np.float16)), bits(x))
+    comm.Iallgather(send.data, count, gathered.data, count, 3)
+    comm.Wait(3)
+    comm.Reduce_Scatter_block(gathered.data, shard.data, count)
+    assert np.array_equal(bits(shard.download(np.float16)), bits(x))
+    comm.finalize()
+
+
+def test_error_behaviour(dl):
+    comm = dl.B200Communicator([0], num_slots=2, dtype=0)
+    t = dl.Tensor(16, 0)
+    with pytest.raises(dl.DlnbError):
+        comm.Iallreduce(t.data, t.data, 16, 2)  # slot out of range
+    with pytest.raises(dl.DlnbError):
+        dl.B200Communicator([1], 1, 0)  # rank outside world
+    comm.Iallreduce(t.data, t.data, 0, 0)  # empty message is a no-op
+    comm.WaitAll(2)
+    comm.finalize()
+
+
+def test_spin_kernel_duration(dl):
+    a, b = dl.spin_calibrate()
+    assert 0 <= a < 50 and 0.9 < b < 1.1, (a, b)
+    for want_us in (50.0, 1000.0, 20000.0):
+        dl.iter_begin()
+        for _ in range(4):
+            dl.compute_spin(want_us)
+        ms = dl.iter_end()
+        got = ms * 1000 / 4
+        assert abs(got - want_us) <= max(5.0, 0.02 * want_us), (want_us, got)
+
+
+def test_collective_waits_for_compute(dl):
+    """A collective enqueued after a spin may not start before it ends (event chain)."""
+    comm = dl.B200Communicator([0], num_slots=1, dtype=0)
+    t, u = dl.Tensor(1 << 20, 0), dl.Tensor(1 << 20, 0)
+    dl.iter_begin()
+    dl.compute_spin(30000.0)
+    comm.Iallreduce(t.data, u.data, 1 << 20, 0)
+    comm.WaitAll(1)
+    ms = dl.iter_end()
+    assert ms >= 29.0, ms
+    comm.finalize()

@@ -1,0 +1,85 @@
+"""Collective micro-sweep through the C ABI (device-timed, slot events).
+
+Single process: world=1 (HBM copy path). Under `torchrun`/dlnb_launch (RANK, WORLD_SIZE
+set): the real multi-GPU kernels; rank 0 prints. busBW follows the nccl-tests
+convention: allreduce 2(n-1)/n*S/t, allgather/reduce-scatter (n-1)/n*S_tot/t;
+at n=1: 2*S/t of HBM traffic.
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from dlnetbench_b200 import capi  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--op", default="allreduce", choices=["allreduce", "allgather", "reduce_scatter"])
+    ap.add_argument("--dtype", default="f16", choices=["f32", "f16", "bf16"])
+    ap.add_argument("--min-bytes", type=int, default=1 << 10)
+    ap.add_argument("--max-bytes", type=int, default=1 << 30)
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--ctas", default="0")
+    ap.add_argument("--algo", type=int, default=0)
+    ap.add_argument("--threads", type=int, default=512)
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", os.environ.get("DLNB_RANK", 0)))
+    world = int(os.environ.get("WORLD_SIZE", os.environ.get("DLNB_WORLD", 1)))
+    capi.init(rank, world)
+    dt = {"f32": capi.F32, "f16": capi.F16, "bf16": capi.BF16}[a.dtype]
+    esz = capi.DTYPE_SIZE[dt]
+    comm = capi.B200Communicator(list(range(world)), num_slots=a.iters, dtype=dt)
+    comm.set("algo", a.algo)
+    comm.set("threads", a.threads)
+    # ring of buffers larger than L2 so no iteration finds its input cached
+    rows = []
+    size = a.min_bytes
+    while size <= a.max_bytes:
+        count = size // esz
+        if a.op == "allreduce":
+            sc, rc = count, count
+        elif a.op == "allgather":
+            sc, rc = count // world, (count // world) * world
+        else:
+            sc, rc = (count // world) * world, count // world
+        nbuf = max(2, min(a.iters, (300 << 20) // max(size, 1) + 1))
+        send = [capi.Tensor(max(sc, 1), dt) for _ in range(nbuf)]
+        recv = [capi.Tensor(max(rc, 1), dt) for _ in range(nbuf)]
+        for t in send:
+            t.fill(capi.PAT_INT, 0, rank)
+        for ctas in [int(c) for c in a.ctas.split(",")]:
+            comm.set("ctas", ctas)
+            for rep in range(2):  # first pass = warm-up
+                for i in range(a.iters):
+                    s, r = send[i % nbuf], recv[i % nbuf]
+                    if a.op == "allreduce":
+                        comm.Iallreduce(s.data, r.data, sc, i)
+                    elif a.op == "allgather":
+                        comm.Iallgather(s.data, sc, r.data, sc, i)
+                    else:
+                        capi.check(capi.lib().dlnb_ireduce_scatter(comm.h, s.data, r.data, rc, i))
+                comm.WaitAll(a.iters)
+            ms = sorted(comm.slot_ms(i) for i in range(a.iters))
+            med = ms[len(ms) // 2]
+            if world == 1:
+                bus = 2 * sc * esz / (med * 1e-3) / 1e9
+            elif a.op == "allreduce":
+                bus = 2 * (world - 1) / world * sc * esz / (med * 1e-3) / 1e9
+            else:
+                bus = (world - 1) / world * max(sc, rc) * esz / (med * 1e-3) / 1e9
+            row = dict(op=a.op, dtype=a.dtype, world=world, bytes=sc * esz if a.op != "reduce_scatter" else sc * esz,
+                       ctas=ctas, us_med=med * 1e3, us_min=ms[0] * 1e3, busbw_GBps=bus)
+            rows.append(row)
+            if rank == 0:
+                print(json.dumps(row), flush=True)
+        size *= 4
+    if rank == 0 and a.out:
+        json.dump(rows, open(a.out, "w"), indent=1)
+    capi.finalize()
+
+
+if __name__ == "__main__":
+    main()
