@@ -151,6 +151,7 @@ struct State {
     // emulation scratch (single-GPU n-rank mode)
     uint32_t *emu_flags = nullptr;
     CommCtl *emu_ctl = nullptr;
+    int emu_last_n = 0;
     // spin
     long spin_ctas = 1, spin_threads = 32, slot_timing = 1;
     double spin_overhead_us = 0.0, spin_slope = 1.0;
@@ -690,8 +691,10 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
 }
 
 static int check_watchdog() {
-    if (G.host_error && *(volatile uint32_t *)G.host_error)
+    if (G.host_error && *(volatile uint32_t *)G.host_error) {
+        *(volatile uint32_t *)G.host_error = 0; // reported once; the caller decides whether to go on
         return fail("cross-GPU flag barrier timed out: a peer rank is dead or out of order");
+    }
     return 0;
 }
 
@@ -900,7 +903,14 @@ static int emu(int op, int nranks, const void *const *send, void *const *recv, s
         CU_TRY(cudaMalloc((void **)&G.emu_flags, MAXR * FLAG_BYTES_PER_COMM));
         CU_TRY(cudaMemset(G.emu_flags, 0, MAXR * FLAG_BYTES_PER_COMM));
         CU_TRY(cudaMalloc((void **)&G.emu_ctl, MAXR * sizeof(CommCtl)));
-        CU_TRY(cudaMemset(G.emu_ctl, 0, MAXR * sizeof(CommCtl)));
+    }
+    // A call with another nranks leaves the virtual ranks at different generations:
+    // restart all of them from generation 0 when the group size changes (same-size
+    // calls keep counting, which is what the multi-GPU path does).
+    if (G.emu_last_n != nranks) {
+        CU_TRY(cudaMemsetAsync(G.emu_flags, 0, MAXR * FLAG_BYTES_PER_COMM, G.s_comm));
+        CU_TRY(cudaMemsetAsync(G.emu_ctl, 0, MAXR * sizeof(CommCtl), G.s_comm));
+        G.emu_last_n = nranks;
     }
     EmuViews ev;
     memset(&ev, 0, sizeof(ev));
