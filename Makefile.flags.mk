@@ -1,0 +1,34 @@
+# -------------------------
+# Makefile.flags.mk
+# Turns BACKEND_<config> into CXXFLAGS_<config> / LDFLAGS_<config> / LDLIBS_<config>.
+#
+# Backends of this tree:
+#   b200         the product: host code is plain C++17 over the C ABI in include/dlnb.h,
+#                linked against dlnetbench_b200/libdlnb.so (built by its own Makefile with
+#                nvcc -gencode arch=compute_100a,code=sm_100a). No external packages.
+#   mpi_cpu_ref  the reference's sources compiled by oracle/Makefile (checker / CPU baseline).
+# The reference's other backends (nccl, rccl, oneccl, mpi_gpu_cuda, mpi_gpu_hip) are not
+# built here; NCCL is only a comparison line (tools/nccl_compare.py).
+# -------------------------
+
+REPO_ROOT  := $(dir $(abspath $(lastword $(MAKEFILE_LIST))))
+DLNB_DIR   := $(REPO_ROOT)dlnetbench_b200
+DLNB_LIB   := $(DLNB_DIR)/libdlnb.so
+NVCC       ?= nvcc
+
+define backend_flags
+CXXFLAGS_$(1) := -O3 -std=c++17 -Wall
+LDFLAGS_$(1)  :=
+LDLIBS_$(1)   := -lpthread -ldl
+ifeq ($$(BACKEND_$(1)),b200)
+CXXFLAGS_$(1) += -I$(REPO_ROOT)include -DPROXY_ENABLE_B200
+LDFLAGS_$(1)  += -L$(DLNB_DIR) -Wl,-rpath,'$$$$ORIGIN/../../../../dlnetbench_b200' -Wl,-rpath,$(DLNB_DIR)
+LDLIBS_$(1)   += -ldlnb
+NEEDS_DLNB_$(1) := 1
+endif
+endef
+
+$(foreach cfg,$(CONFIGS) $(MAKECMDGOALS),$(if $(BACKEND_$(cfg)),$(eval $(call backend_flags,$(cfg)))))
+
+$(DLNB_LIB): $(wildcard $(DLNB_DIR)/csrc/*.cu $(DLNB_DIR)/csrc/*.cuh $(DLNB_DIR)/csrc/*.cpp $(DLNB_DIR)/csrc/*.hpp $(DLNB_DIR)/csrc/*.inc) $(REPO_ROOT)include/dlnb.h
+	$(MAKE) --no-print-directory -C $(DLNB_DIR)/csrc NVCC=$(NVCC)

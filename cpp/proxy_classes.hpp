@@ -1,0 +1,162 @@
+// cpp/proxy_classes.hpp — communicator interface, the B200 backend and Tensor.
+//
+// Drop-in for the reference's cpp/proxy_classes.hpp: `ProxyCommunicator` has the same 15
+// virtuals with the same names, argument meaning and (void) error behaviour (:30-51), and
+// `Tensor<T, Device>` the same public fields and RAII contract (:381-444). The backends of
+// the reference (MPICommunicator :53-133, CCLCommunicator :135-253, OneCCLCommunicator
+// :255-342) are replaced by ONE: B200Communicator, every method a single call into the C
+// ABI of libdlnb.so (include/dlnb.h), whose kernels read and write peer HBM directly.
+#ifndef PROXY_CLASSES_HPP
+#define PROXY_CLASSES_HPP
+
+#include <dlnb.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <unistd.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+class ProxyCommunicator {
+  public:
+    virtual void Iallreduce(const void *sendbuf, void *recvbuf, int count, int index) = 0;
+    virtual void Allreduce(const void *sendbuf, void *recvbuf, int count) = 0;
+    virtual void Iallgather(const void *sendbuf, int sendcount, void *recvbuf, int recvcount, int index) = 0;
+    virtual void Allgather(const void *sendbuf, int sendcount, void *recvbuf, int recvcount) = 0;
+    virtual void Reduce_Scatter_block(const void *sendbuf, void *recvbuf, int recvcount) = 0;
+    virtual void Alltoall(const void *sendbuf, int sendcount, void *recvbuf, int recvcount) = 0;
+    virtual void Barrier() = 0;
+    virtual void WaitAll(int num_waits) = 0;
+    virtual void Wait(int index) = 0;
+    virtual void finalize() = 0;
+    virtual void send(const void *buf, int count, int dest) = 0;
+    virtual void recv(void *buf, int count, int source) = 0;
+    virtual void Isend(const void *buf, int count, int dest, int index) = 0;
+    virtual void Irecv(void *buf, int count, int source, int index) = 0;
+    virtual std::string get_name() = 0;
+    virtual ~ProxyCommunicator() {}
+};
+
+// Errors do not propagate through the void interface: print "[rank r] what" and exit, as the
+// reference does through CCUTILS_GPU_CHECK / MPI_ERRORS_ARE_FATAL.
+#define B200_CHECK(call)                                                                           \
+    do {                                                                                           \
+        if ((call) != 0) {                                                                         \
+            fprintf(stderr, "[rank %d] %s failed: %s\n", dlnb_rank(), #call, dlnb_last_error());   \
+            fflush(stderr);                                                                        \
+            _exit(1);                                                                              \
+        }                                                                                          \
+    } while (0)
+
+class B200Communicator : public ProxyCommunicator {
+  public:
+    // `group` = world ranks of this communicator in group order (what MPI_Comm_split /
+    // ncclCommSplit produce in fsdp.cpp:258-283); `num_slots` = the reference's
+    // num_requests / num_streams; `dtype` = a dlnb_dtype.
+    B200Communicator(const std::vector<int> &group, int num_slots, int dtype) {
+        B200_CHECK(dlnb_comm_create(group.data(), (int)group.size(), num_slots > 0 ? num_slots : 1, dtype, &comm));
+        rank = dlnb_comm_rank(comm);
+        comm_size = dlnb_comm_size(comm);
+    }
+
+    void Iallreduce(const void *sendbuf, void *recvbuf, int count, int index) override {
+        B200_CHECK(dlnb_iallreduce(comm, sendbuf, recvbuf, elems(count), index));
+    }
+    void Allreduce(const void *sendbuf, void *recvbuf, int count) override {
+        B200_CHECK(dlnb_allreduce(comm, sendbuf, recvbuf, elems(count)));
+    }
+    void Iallgather(const void *sendbuf, int sendcount, void *recvbuf, int recvcount, int index) override {
+        same(sendcount, recvcount);
+        B200_CHECK(dlnb_iallgather(comm, sendbuf, recvbuf, elems(sendcount), index));
+    }
+    void Allgather(const void *sendbuf, int sendcount, void *recvbuf, int recvcount) override {
+        same(sendcount, recvcount);
+        B200_CHECK(dlnb_allgather(comm, sendbuf, recvbuf, elems(sendcount)));
+    }
+    void Reduce_Scatter_block(const void *sendbuf, void *recvbuf, int recvcount) override {
+        B200_CHECK(dlnb_reduce_scatter(comm, sendbuf, recvbuf, elems(recvcount)));
+    }
+    void WaitAll(int num_waits) override { B200_CHECK(dlnb_waitall(comm, num_waits)); }
+    void Wait(int index) override { B200_CHECK(dlnb_wait(comm, index)); }
+    void Barrier() override { B200_CHECK(dlnb_barrier(comm)); }
+    void finalize() override {
+        if (comm) B200_CHECK(dlnb_comm_destroy(comm));
+        comm = nullptr;
+    }
+    std::string get_name() override { return "B200P2P"; }
+
+    // Pipeline / expert-parallel traffic: used only by the hybrid proxies, which are outside
+    // this build (the data-parallel drivers never call them — no call site in dp.cpp/fsdp.cpp).
+    void Alltoall(const void *, int, void *, int) override { unsupported("Alltoall"); }
+    void send(const void *, int, int) override { unsupported("send"); }
+    void recv(void *, int, int) override { unsupported("recv"); }
+    void Isend(const void *, int, int, int) override { unsupported("Isend"); }
+    void Irecv(void *, int, int, int) override { unsupported("Irecv"); }
+
+    // additions
+    void set(const char *key, long v) { B200_CHECK(dlnb_comm_set(comm, key, v)); }
+    float slot_ms(int index) {
+        float ms = 0;
+        B200_CHECK(dlnb_slot_elapsed(comm, index, &ms));
+        return ms;
+    }
+    dlnb_comm_t handle() const { return comm; }
+    int size() const { return comm_size; }
+
+  private:
+    static size_t elems(int count) {
+        if (count < 0) {
+            // the reference narrows uint64_t sizes to int (dp.cpp:99, fsdp.cpp:88): diagnose the wrap
+            fprintf(stderr, "[rank %d] element count %d is negative: the message exceeds INT_MAX elements; "
+                            "use more buckets / units\n", dlnb_rank(), count);
+            _exit(1);
+        }
+        return (size_t)count;
+    }
+    static void same(int a, int b) {
+        if (a != b) {
+            fprintf(stderr, "[rank %d] allgather with sendcount %d != recvcount %d is not supported\n", dlnb_rank(), a, b);
+            _exit(1);
+        }
+    }
+    [[noreturn]] static void unsupported(const char *what) {
+        fprintf(stderr, "[rank %d] B200Communicator::%s is not part of the data-parallel build\n", dlnb_rank(), what);
+        _exit(1);
+    }
+    dlnb_comm_t comm = nullptr;
+    int comm_size = 1;
+    int rank = 0;
+};
+
+enum class Device { CPU, GPU };
+
+// Contiguous zero-filled buffer. GPU tensors live in libdlnb's symmetric arena, so that every
+// rank's kernels can address every other rank's copy (construction is collective: same order
+// and sizes on all ranks, which dp.cpp:229-232 / fsdp.cpp:348-354 already guarantee).
+template <typename T, Device device = Device::CPU> class Tensor {
+  public:
+    T *data = nullptr;
+    uint64_t size = 0;
+
+    explicit Tensor(uint64_t size_) : size(size_) {
+        if constexpr (device == Device::CPU) {
+            data = static_cast<T *>(calloc(size ? size : 1, sizeof(T)));
+            if (!data) throw std::runtime_error("Failed to allocate CPU memory");
+        } else {
+            void *p = nullptr;
+            B200_CHECK(dlnb_symm_alloc(size * sizeof(T), &p));
+            data = static_cast<T *>(p);
+        }
+    }
+    Tensor(const Tensor &) = delete;
+    Tensor &operator=(const Tensor &) = delete;
+    ~Tensor() {
+        if (!data) return;
+        if constexpr (device == Device::CPU) free(data);
+        else dlnb_symm_free(data);
+    }
+};
+
+#endif // PROXY_CLASSES_HPP

@@ -473,10 +473,11 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
     c->n = nranks;
     c->dtype = dtype;
     c->num_slots = std::max(1, num_slots);
-    c->ev_start.resize(c->num_slots);
-    c->ev_end.resize(c->num_slots);
-    c->slot_used.assign(c->num_slots, 0);
-    for (int i = 0; i < c->num_slots; ++i) {
+    // one extra, internal slot (index num_slots) for the blocking calls
+    c->ev_start.resize(c->num_slots + 1);
+    c->ev_end.resize(c->num_slots + 1);
+    c->slot_used.assign(c->num_slots + 1, 0);
+    for (int i = 0; i <= c->num_slots; ++i) {
         CU_TRY(cudaEventCreate(&c->ev_start[i]));
         CU_TRY(cudaEventCreate(&c->ev_end[i]));
     }
@@ -649,7 +650,8 @@ static int join_streams() {
 static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count, int slot) {
     NEED_INIT();
     if (!c) return fail("null communicator");
-    if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range (communicator has %d)", slot, c->num_slots);
+    if (slot == -1) slot = c->num_slots; // internal slot of the blocking calls
+    else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range (communicator has %d)", slot, c->num_slots);
     if (count && (!send || !recv)) return fail("null buffer");
     const size_t esz = dtype_size(c->dtype);
     if (op == OP_AR1 || op == OP_AR2) {
@@ -710,7 +712,8 @@ extern "C" int dlnb_ireduce_scatter(dlnb_comm_t c, const void *send, void *recv,
 extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
     NEED_INIT();
     if (!c) return fail("null communicator");
-    if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
+    if (slot == -1) slot = c->num_slots;
+    else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
     if (!c->slot_used[slot]) return 0;
     CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
     return check_watchdog();
@@ -732,21 +735,22 @@ extern "C" int dlnb_barrier(dlnb_comm_t c) {
     return check_watchdog();
 }
 extern "C" int dlnb_allreduce(dlnb_comm_t c, const void *send, void *recv, size_t count) {
-    if (coll(c, OP_AR2, send, recv, count, 0)) return 1;
-    return dlnb_wait(c, 0);
+    if (coll(c, OP_AR2, send, recv, count, -1)) return 1;
+    return dlnb_wait(c, -1);
 }
 extern "C" int dlnb_allgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount) {
-    if (coll(c, OP_AG, send, recv, sendcount, 0)) return 1;
-    return dlnb_wait(c, 0);
+    if (coll(c, OP_AG, send, recv, sendcount, -1)) return 1;
+    return dlnb_wait(c, -1);
 }
 extern "C" int dlnb_reduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount) {
-    if (coll(c, OP_RS, send, recv, recvcount, 0)) return 1;
-    return dlnb_wait(c, 0);
+    if (coll(c, OP_RS, send, recv, recvcount, -1)) return 1;
+    return dlnb_wait(c, -1);
 }
 extern "C" int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms) {
     NEED_INIT();
     if (!c || !ms) return fail("null argument");
-    if (slot < 0 || slot >= c->num_slots || !c->slot_used[slot]) return fail("slot %d has no recorded collective", slot);
+    if (slot == -1) slot = c->num_slots; // the most recent blocking call
+    if (slot < 0 || slot > c->num_slots || !c->slot_used[slot]) return fail("slot %d has no recorded collective", slot);
     CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
     CU_TRY(cudaEventElapsedTime(ms, c->ev_start[slot], c->ev_end[slot]));
     return 0;

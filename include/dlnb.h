@@ -134,7 +134,8 @@ uint64_t dlnb_launch_count(void);
  * ccutils CCUTILS_MPI_TIMER_*): cudaEvent pair spanning both streams. */
 int dlnb_iter_begin(void);
 int dlnb_iter_end(float *ms);
-/* device time of the most recent collective recorded in `slot` (ms) */
+/* device time of the most recent collective recorded in `slot` (ms); slot -1 = the most
+ * recent BLOCKING call (those use an internal slot, never one of the caller's) */
 int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms);
 
 /* ---- buffer helpers (tests, bench, end-to-end path) ----------------------------- */

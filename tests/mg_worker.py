@@ -1,0 +1,133 @@
+"""One rank of the multi-GPU parity run (started N times by bin/dlnb_launch or torchrun).
+
+Checks, through the C ABI on real peer memory: allreduce (one-shot, two-shot, auto),
+allgather, reduce-scatter for fp32/fp16/bf16 at edge counts and BASELINE-shaped counts,
+against (a) the CPU oracle on the host for small sizes and (b) the closed-form on-device
+verifier for large ones; sub-communicators as fsdp builds them (unit groups / replica
+groups); back-to-back launches with changing grids (flag generations). Exit code 0 = pass.
+"""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from dlnetbench_b200 import capi  # noqa: E402
+from oracle import oracle_capi as oracle  # noqa: E402
+
+NPDT = {0: np.float32, 1: np.float16, 2: np.uint16}
+
+
+def bits(a):
+    return a.view(np.uint32) if a.dtype == np.float32 else a.view(np.uint16)
+
+
+def main():
+    rank = int(os.environ.get("DLNB_RANK", os.environ.get("RANK", 0)))
+    world = int(os.environ.get("DLNB_WORLD", os.environ.get("WORLD_SIZE", 1)))
+    quick = "--quick" in sys.argv
+    capi.init(rank, world)
+    fails = []
+
+    def expect(ok, what):
+        if not ok:
+            fails.append(what)
+            print(f"[rank {rank}] FAIL {what}", flush=True)
+
+    small = [1, 7, 8, 15, 4095, 4097, 65536 + 17]
+    big = [1_000_003, 8_388_608] if quick else [1_000_003, 33_554_432 + 5, 110_240_167]
+    groups = {"world": list(range(world))}
+    if world >= 4:  # fsdp with sharding_factor = world/2: unit groups and replica groups
+        F = world // 2
+        groups["unit"] = [rank // F * F + i for i in range(F)]
+        groups["replica"] = [rank % F + i * F for i in range(world // F)]
+
+    for dtype in (0, 1, 2):
+        comms = {k: capi.B200Communicator(g, num_slots=4, dtype=dtype) for k, g in groups.items()}
+        for gname, comm in comms.items():
+            g = groups[gname]
+            n, me = len(g), g.index(rank)
+            for count in small + (big if gname == "world" else big[:1]):
+                kinds = (1, 2) if count <= 65536 + 17 else (2,)
+                for kind in kinds:
+                    seed = 1234 + count % 7
+                    # ---- allreduce, every algorithm
+                    send, recv = capi.Tensor(count, dtype), capi.Tensor(count, dtype)
+                    send.fill(kind, seed, rank)
+                    for algo in (capi.ALGO_ONESHOT, capi.ALGO_TWOSHOT, capi.ALGO_AUTO):
+                        if algo == capi.ALGO_ONESHOT and count > 40_000_000:
+                            continue
+                        comm.set("algo", algo)
+                        recv.fill(0)
+                        comm.Iallreduce(send.data, recv.data, count, 1)
+                        comm.WaitAll(4)
+                        bad = capi.verify_sum_pattern(recv.data, count, 0, dtype, kind, seed, g)
+                        expect(bad == 0, f"allreduce {gname} dtype={dtype} algo={algo} count={count} kind={kind}: {bad} mismatches")
+                    if count <= 65536 + 17:
+                        xs = [oracle.fill_pattern(count, dtype, kind, seed, r) for r in g]
+                        want = oracle.allreduce(xs, dtype)
+                        expect(np.array_equal(bits(recv.download(NPDT[dtype])), bits(want)), f"allreduce vs oracle {gname} {dtype} {count}")
+                    comm.set("algo", capi.ALGO_AUTO)
+                    # ---- allgather: every block r must be rank g[r]'s pattern
+                    gathered = capi.Tensor(count * n, dtype)
+                    comm.Iallgather(send.data, count, gathered.data, count, 2)
+                    comm.Wait(2)
+                    for r in range(n):
+                        bad = capi.verify_sum_pattern(gathered.offset(r * count), count, 0, dtype, kind, seed, [g[r]])
+                        expect(bad == 0, f"allgather {gname} dtype={dtype} count={count} block={r}: {bad} mismatches")
+                    # ---- reduce-scatter of the gathered buffer's shape: send n*count, receive block `me`
+                    rs_send, rs_recv = capi.Tensor(count * n, dtype), capi.Tensor(count, dtype)
+                    rs_send.fill(kind, seed, rank)
+                    comm.Reduce_Scatter_block(rs_send.data, rs_recv.data, count)
+                    bad = capi.verify_sum_pattern(rs_recv.data, count, me * count, dtype, kind, seed, g)
+                    expect(bad == 0, f"reduce_scatter {gname} dtype={dtype} count={count}: {bad} mismatches")
+                    if count <= 4097:
+                        xs = [oracle.fill_pattern(count * n, dtype, kind, seed, r) for r in g]
+                        want = oracle.reduce_scatter_block(xs, me, count, dtype)
+                        expect(np.array_equal(bits(rs_recv.download(NPDT[dtype])), bits(want)), f"reduce_scatter vs oracle {gname} {dtype} {count}")
+        # ---- generations: many launches, grid changing every time, results checked at the end
+        comm = comms["world"]
+        count = 2_000_003
+        send = capi.Tensor(count, dtype)
+        send.fill(2, 5, rank)
+        outs = [capi.Tensor(count, dtype) for _ in range(4)]
+        for it in range(40):
+            comm.set("ctas", [1, 7, 32, 64, 3, 128][it % 6])
+            comm.set("algo", 1 + it % 2)
+            comm.Iallreduce(send.data, outs[it % 4].data, count, it % 4)
+        comm.WaitAll(4)
+        for o in outs:
+            expect(capi.verify_sum_pattern(o.data, count, 0, dtype, 2, 5, list(range(world))) == 0, f"generations dtype={dtype}")
+        comm.set("ctas", 0)
+        comm.set("algo", 0)
+        for c in comms.values():
+            c.finalize()
+
+    # ---- a dp-shaped overlapped iteration: spin -> allreduce chains, device-timed
+    comm = capi.B200Communicator(list(range(world)), num_slots=8, dtype=capi.F16)
+    count = 4_000_001
+    send = [capi.Tensor(count, capi.F16) for _ in range(8)]
+    recv = [capi.Tensor(count, capi.F16) for _ in range(8)]
+    for t in send:
+        t.fill(1, 0, rank)
+    capi.spin_calibrate()
+    capi.iter_begin()
+    capi.compute_spin(2000.0)
+    for i in range(8):
+        capi.compute_spin(500.0)
+        comm.Iallreduce(send[i].data, recv[i].data, count, i)
+    comm.WaitAll(8)
+    ms = capi.iter_end()
+    for t in recv:
+        expect(capi.verify_sum_pattern(t.data, count, 0, capi.F16, 1, 0, list(range(world))) == 0, "dp iteration result")
+    expect(6.0 <= ms < 8.0, f"dp iteration took {ms:.3f} ms for 6 ms of emulated compute")
+    comm.finalize()
+
+    arena = capi.lib().dlnb_arena_kind().decode()
+    capi.finalize()
+    print(f"[rank {rank}/{world}] arena={arena} iteration={ms:.3f} ms failures={len(fails)}", flush=True)
+    sys.exit(1 if fails else 0)
+
+
+if __name__ == "__main__":
+    main()
