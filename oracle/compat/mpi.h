@@ -189,6 +189,10 @@ inline void allgather_bytes(const char *send, size_t sbytes, char *recv, Comm *c
 inline void allgatherv_bytes(const char *send, size_t sbytes, char *recv, const int *counts, const int *displs,
                              size_t esz, Comm *c) {
     const int n = c->size, me = c->rank;
+    if (n == 1) {
+        memcpy(recv + (size_t)displs[0] * esz, send, sbytes);
+        return;
+    }
     if (sbytes > SLOT_BYTES) die("MPI_Allgatherv: message larger than the staging slot");
     memcpy(slot_in(c->world_rank[me]), send, sbytes);
     barrier(c);

@@ -1,0 +1,155 @@
+"""CPU suite, part 2: the boundary and the host logic — no GPU, no compute calls.
+
+ * libdlnb.so loads here and exports every symbol include/dlnb.h declares;
+ * without a GPU the product path fails loudly (no CPU fallback anywhere);
+ * the rendezvous (abstract unix socket hub + SCM_RIGHTS fd exchange) works across processes;
+ * the launcher, the drivers' CLI and exit codes behave like the reference's;
+ * the reference's own dp/fsdp (oracle/_ref) run multi-rank on host cores and their output
+   parses with dlnetbench_b200.parser — that is also the multi-process (world_size 2) CPU path
+   of bench.py's reference arm.
+"""
+import ctypes
+import json
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+from conftest import GPU_COUNT, ROOT
+
+BIN = os.path.join(ROOT, "bin", "b200", "cpp", "data_parallel")
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def built():
+    import __graft_entry__ as g
+
+    g.build()
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    from dlnetbench_b200 import capi
+
+    names = capi.declared_symbols()
+    assert len(names) >= 45 and "dlnb_iallreduce" in names and "dlnb_emu_allreduce" in names
+    lib = ctypes.CDLL(capi.LIB_PATH)
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    # and nothing is exported beyond the header (the ABI is exactly the header)
+    out = subprocess.run(["nm", "-D", "--defined-only", capi.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (dlnb_[a-z0-9_]+)", out))
+    assert exported == set(names), exported ^ set(names)
+
+
+def test_header_cites_the_reference_for_every_replaced_call():
+    text = open(os.path.join(ROOT, "include", "dlnb.h")).read()
+    for needle in ("proxy_classes.hpp:32", "proxy_classes.hpp:34-35", "proxy_classes.hpp:38", "proxy_classes.hpp:41-43",
+                   "dp.cpp:93,98", "utils.hpp:74-117", "proxy_classes.hpp:401-405"):
+        assert needle in text, needle
+    assert "torch" not in text.lower()
+
+
+@pytest.mark.skipif(GPU_COUNT > 0, reason="checks the no-GPU failure mode")
+def test_no_gpu_means_loud_failure_not_fallback():
+    from dlnetbench_b200 import capi
+
+    with pytest.raises(capi.DlnbError) as e:
+        capi.init(0, 1, 0, "nogpu")
+    assert "CUDA" in str(e.value) or "device" in str(e.value)
+    res = subprocess.run([os.path.join(BIN, "dp"), "gpt2_l_16_bfloat16", "10", "."], cwd=ROOT, capture_output=True, text=True)
+    assert res.returncode == 1 and "[rank 0]" in res.stderr and "dlnb_init" in res.stderr
+    assert "#CCUTILS_SECTION" not in res.stdout
+
+
+def test_product_never_touches_the_oracle():
+    """Nothing the product ships may import, include, link or execute anything under oracle/."""
+    bad = re.compile(r"import\s+oracle|from\s+oracle|oracle/|oracle_capi|dlnb_oracle|libdlnb_oracle")
+    for top in ("dlnetbench_b200", "cpp", "include", "tools"):
+        for base, _, files in os.walk(os.path.join(ROOT, top)):
+            if os.sep + "build" in base:
+                continue
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".inc", ".h", ".mk")) or f.startswith("Makefile"):
+                    text = open(os.path.join(base, f), errors="ignore").read()
+                    assert not bad.search(text), os.path.join(base, f)
+
+
+def test_rendezvous_allgather_and_fd_exchange(tmp_path):
+    exe = tmp_path / "bootstrap_test"
+    subprocess.check_call(["g++", "-O1", "-std=c++17", "-o", str(exe), os.path.join(ROOT, "tests", "cpp", "bootstrap_test.cpp"),
+                           os.path.join(ROOT, "dlnetbench_b200", "csrc", "bootstrap.cpp")])
+    for n in (2, 8):
+        res = subprocess.run([str(exe), str(n)], capture_output=True, text=True, timeout=60)
+        assert res.returncode == 0 and "OK" in res.stdout, res.stdout + res.stderr
+
+
+def test_launcher_sets_rank_env_and_propagates_failure():
+    launch = os.path.join(ROOT, "bin", "dlnb_launch")
+    res = subprocess.run([launch, "-n", "3", "sh", "-c", "echo r=$DLNB_RANK w=$DLNB_WORLD s=$DLNB_SESSION"], capture_output=True, text=True)
+    lines = sorted(res.stdout.split())
+    assert res.returncode == 0
+    assert [x for x in lines if x.startswith("r=")] == ["r=0", "r=1", "r=2"]
+    assert len({x for x in lines if x.startswith("s=")}) == 1
+    res = subprocess.run([launch, "-n", "2", "sh", "-c", "test $DLNB_RANK = 0 || exit 7"], capture_output=True, text=True)
+    assert res.returncode == 7
+    assert subprocess.run([launch, "-n", "9", "true"], capture_output=True).returncode == 2
+
+
+@pytest.mark.parametrize("prog,nreq", [("dp", 3), ("fsdp", 4), ("dp_loop", 3), ("fsdp_loop", 4)])
+def test_driver_cli_matches_reference_conventions(prog, nreq):
+    exe = os.path.join(BIN, prog)
+    res = subprocess.run([exe, "-h"], capture_output=True, text=True, cwd=ROOT)
+    assert res.returncode in (1, 255)  # help -> 1 (dp.cpp:132-135); fsdp with argc<5 -> -1 (fsdp.cpp:198-202)
+    assert "Usage" in res.stdout
+    args = ["gpt2_l_16_bfloat16", "4", "2", "."][: nreq - 1] if prog.startswith("fsdp") else ["gpt2_l_16_bfloat16", "4"]
+    res = subprocess.run([exe, *args], capture_output=True, text=True, cwd=ROOT)  # one positional short
+    assert res.returncode in (1, 255) and "Usage" in res.stdout
+    full = ["nope_model", "4", "1", "."] if prog.startswith("fsdp") else ["nope_model", "4", "."]
+    res = subprocess.run([exe, *full], capture_output=True, text=True, cwd=ROOT)
+    assert res.returncode == 255 and "model stats file does not exist" in res.stderr  # return -1 (dp.cpp:145-148)
+
+
+def test_fsdp_rejects_sharding_factor_not_dividing_world():
+    res = subprocess.run([os.path.join(BIN, "fsdp"), "gpt2_l_16_bfloat16", "4", "3", "."], capture_output=True, text=True, cwd=ROOT,
+                         env={**os.environ, "DLNB_WORLD": "4", "DLNB_RANK": "0"})
+    assert res.returncode == 1 and "multiple of the sharding factor" in res.stderr
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(REF, "dp")), reason="oracle/_ref not built (needs /root/reference at build time)")
+def test_reference_proxies_run_multirank_on_cpu_and_parse():
+    from dlnetbench_b200.parser import parse_sections
+
+    mpirun = os.path.join(REF, "dlnb_mpirun")
+    res = subprocess.run([mpirun, "-n", "2", os.path.join(REF, "dp"), "vit_b_16_bfloat16", "7", ".", "-w", "0", "-r", "2"],
+                         capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert res.returncode == 0, res.stderr
+    sec = parse_sections(res.stdout)["dp"]
+    assert sec["title"] == "Data Parallelism" and sec["json_data"]["backend"] == "MPI" and sec["json_data"]["world_size"] == 2
+    assert sorted(sec["rank_outputs"]) == [0, 1] and len(sec["rank_outputs"][1]["runtimes"]) == 2
+    res = subprocess.run([mpirun, "-n", "4", os.path.join(REF, "fsdp"), "vit_b_16_bfloat16", "3", "2", ".", "-w", "0", "-r", "1"],
+                         capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert res.returncode == 0, res.stderr
+    sec = parse_sections(res.stdout)["fsdp"]
+    assert sec["json_data"]["num_replicas"] == 2 and len(sec["rank_outputs"][3]["reduce_scatter"]) == 3
+    assert len(sec["rank_outputs"][0]["barrier"]) == 1
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(REF, "dp")), reason="oracle/_ref not built")
+def test_bench_reference_arm_two_ranks_on_cpu():
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0",
+                          "--model", "vit_b_16_bfloat16", "--buckets", "5"], capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert res.returncode == 0, res.stderr
+    line = json.loads(res.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["unit"] == "ms" and line["higher_is_better"] is False
+    assert line["cpu_baseline"]["kind"] == "reference" and line["cpu_baseline"]["cores"] == 2
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["value"] > 0
+
+
+def test_bucket_split_in_bench_matches_oracle(oracle):
+    import bench
+
+    for m, n in ((8_030_261_248, 240), (632_404_480, 1000), (774_030_080, 10), (17, 5)):
+        assert bench.bucket_sizes(m, n) == oracle.bucket_sizes(m, n)

@@ -1,0 +1,168 @@
+"""CPU suite, part 1: the oracle against the golden vectors and the reference's own outputs.
+
+tests/golden/ref_collectives_f32.npz and ref_proxy_outputs.json were produced by the REFERENCE
+(its MPICommunicator / dp.cpp / fsdp.cpp compiled unmodified against oracle/compat; generator:
+tests/golden/make_golden.py). Nothing here reads /root/reference."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(GOLD, "ref_collectives_f32.npz"))
+
+
+def test_golden_file_covers_every_collective(gold):
+    ops = {k.split("_w")[0] for k in gold.files}
+    assert ops == {"iallreduce", "allreduce", "iallgather", "reduce_scatter"}
+    assert len(gold.files) == 5 * 4 * 2 * 3
+
+
+def _case(key):
+    op, w, k, c = key.rsplit("_", 3)
+    return op, int(w[1:]), int(k[1:]), int(c[1:])
+
+
+def test_oracle_reproduces_reference_collectives_bit_for_bit(oracle, gold):
+    for key in gold.files:
+        op, world, kind, count = _case(key)
+        want = gold[key]
+        if op in ("allreduce", "iallreduce"):
+            xs = [oracle.fill_pattern(count, 0, kind, 1234, r) for r in range(world)]
+            got = oracle.allreduce(xs, 0)
+        elif op == "iallgather":
+            xs = [oracle.fill_pattern(count, 0, kind, 1234, r) for r in range(world)]
+            got = oracle.allgather(xs, 0)
+        else:
+            xs = [oracle.fill_pattern(count * world, 0, kind, 1234, r) for r in range(world)]
+            got = np.concatenate([oracle.reduce_scatter_block(xs, r, count, 0) for r in range(world)])
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), key
+
+
+def test_integer_pattern_sums_are_exact_in_fp16(oracle):
+    n, count = 8, 10007
+    xs16 = [oracle.fill_pattern(count, 1, 1, 0, r) for r in range(n)]
+    xs32 = [x.astype(np.float32) for x in xs16]
+    assert max(np.abs(x).max() for x in xs32) <= 8
+    exact = np.sum(np.stack(xs32).astype(np.int64), axis=0)
+    got = oracle.allreduce(xs16, 1).astype(np.float32)
+    assert np.array_equal(got, exact.astype(np.float32))
+    # any association gives the same bits
+    rev = oracle.allreduce(xs16[::-1], 1)
+    assert np.array_equal(rev.view(np.uint16), oracle.allreduce(xs16, 1).view(np.uint16))
+
+
+def test_random_sums_within_north_star_tolerance(oracle):
+    """2*(n-1)*eps relative error bound of the north star, checked against float64."""
+    for dtype, eps, npdt in ((0, 2.0**-23, np.float32), (1, 2.0**-10, np.float16)):
+        for n in (2, 4, 8):
+            xs = [oracle.fill_pattern(50021, dtype, 2, 9, r) for r in range(n)]
+            got = oracle.allreduce(xs, dtype).astype(np.float64)
+            ref = np.sum(np.stack([x.astype(np.float64) for x in xs]), axis=0)
+            scale = np.sum(np.stack([np.abs(x.astype(np.float64)) for x in xs]), axis=0)
+            assert np.all(np.abs(got - ref) <= 2 * (n - 1) * eps * scale + 1e-30)
+
+
+def test_half_and_bf16_conversions_match_numpy(oracle):
+    L = oracle.lib()
+    allh = np.arange(65536, dtype=np.uint16)
+    finite = np.isfinite(allh.view(np.float16))
+    ref = allh.view(np.float16).astype(np.float32)
+    got = np.array([L.dlnb_oracle_half_to_float(int(h)) for h in allh[finite]], dtype=np.float32)
+    assert np.array_equal(got.view(np.uint32), ref[finite].view(np.uint32))
+    rng = np.random.default_rng(0)
+    f = np.concatenate([rng.standard_normal(3000).astype(np.float32) * s for s in (1e-8, 1e-5, 1e-3, 1, 100, 7e4)]
+                       + [np.array([65519.9, 65520, 65504, 2**-25, 2**-24, 2**-25 * 1.0000001, 0, -0.0, np.inf, -np.inf], np.float32)])
+    hv = ref[finite]
+    hv = np.sort(hv)
+    mid = ((hv[:-1].astype(np.float64) + hv[1:].astype(np.float64)) / 2).astype(np.float32)[::7]
+    f = np.concatenate([f, mid])
+    with np.errstate(over="ignore"):
+        want = f.astype(np.float16).view(np.uint16)
+    got = np.array([L.dlnb_oracle_float_to_half(float(x)) for x in f], dtype=np.uint16)
+    assert np.array_equal(got, want)
+    # bf16: round-to-nearest-even of the top 16 bits
+    u = f[np.isfinite(f)].view(np.uint32)
+    want_bf = ((u.astype(np.uint64) + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+    got_bf = np.array([L.dlnb_oracle_float_to_bf16(float(x)) for x in f[np.isfinite(f)]], dtype=np.uint16)
+    assert np.array_equal(got_bf, want_bf)
+
+
+def test_sizing_rules_match_reference_outputs(oracle):
+    """Bucket/shard sizes and per-unit times as the reference's own binaries printed them."""
+    gold = json.load(open(os.path.join(GOLD, "ref_proxy_outputs.json")))
+    assert {g["prog"] for g in gold} == {"dp", "fsdp"}
+    for g in gold:
+        G = g["global"]
+        st = oracle.parse_model_stats(os.path.join(ROOT, "model_stats", g["args"][0] + ".txt"))
+        if g["prog"] == "dp":
+            n = int(g["args"][1])
+            sizes = oracle.bucket_sizes(st["modelSize"], n)
+            assert sum(sizes) == st["modelSize"] == G["total_model_size_params"]
+            assert G["fwd_rt_whole_model"] == st["avgForwardTime"]
+            assert G["bwd_rt_per_bucket"] == st["avgBackwardTime"] // n
+            avg, std = oracle.msg_stats(sizes)
+            assert G["msg_size_avg_bytes"] == pytest.approx(avg * 4, rel=1e-6)  # the reference's _FLOAT is 4 bytes
+            assert G["msg_size_std_bytes"] == pytest.approx(std * 4, rel=1e-4, abs=1e-3)
+            assert set(g["rank_keys"]) == {"runtimes", "barrier_time", "hostname"}
+        else:
+            u, f = int(g["args"][1]), int(g["args"][2])
+            shards = oracle.shard_sizes(st["modelSize"], u, f)
+            assert G["allgather_msg_size_bytes"] == shards[0] * f * 4
+            assert G["reducescatter_msg_size_bytes"] == shards[0] * 4
+            assert G["num_replicas"] == g["world"] // f
+            assert G["fwd_time_per_unit_us"] == pytest.approx(st["avgForwardTime"] / u, rel=1e-6)
+            assert G["bwd_time_per_unit_us"] == pytest.approx(st["avgBackwardTime"] / u, rel=1e-6)
+            rk = g["rank_keys"]
+            runs = rk["runtime"]
+            assert rk["allgather"] == runs and rk["reduce_scatter"] == runs * u
+            assert rk["allgather_wait_fwd"] == runs * (u - 1) == rk["allgather_wait_bwd"]
+            assert rk["barrier"] == (runs if G["num_replicas"] > 1 else 0)
+            assert ("allreduce_msg_size_bytes" in G) == (G["num_replicas"] > 1)
+
+
+def test_baseline_sizes_and_lower_bounds(oracle):
+    """The numbers BASELINE.md / SURVEY §8a quote for C1..C5."""
+    st = {m: oracle.parse_model_stats(os.path.join(ROOT, "model_stats", m + ".txt"))
+          for m in ("gpt2_l_16_bfloat16", "llama3_8b_64_bfloat16", "vit_h_128_bfloat16", "llama3_70b_16_bfloat16")}
+    assert st["llama3_8b_64_bfloat16"]["modelSize"] == 8_030_261_248
+    assert (st["llama3_8b_64_bfloat16"]["avgForwardTime"], st["llama3_8b_64_bfloat16"]["avgBackwardTime"]) == (3_752_999, 7_505_999)
+    assert oracle.bucket_sizes(774_030_080, 10) == [77_403_008] * 10
+    b = oracle.bucket_sizes(8_030_261_248, 10)
+    assert b[:8] == [803_026_125] * 8 and b[8:] == [803_026_124] * 2
+    v = oracle.bucket_sizes(632_404_480, 1000)
+    assert v.count(632_405) == 480 and v.count(632_404) == 520
+    assert oracle.shard_sizes(8_030_261_248, 32, 8)[0] == 31_368_208
+    assert oracle.shard_sizes(8_030_261_248, 32, 2)[0] == 125_472_832
+    s70 = oracle.shard_sizes(70_553_706_496, 80, 8)
+    assert s70[0] == 110_240_167 and len(s70) == 80
+    lb = lambda m, n: oracle.dp_lower_bound_us(st[m]["avgForwardTime"], st[m]["avgBackwardTime"], n)  # noqa: E731
+    assert lb("gpt2_l_16_bfloat16", 10) == 35_042
+    assert lb("vit_h_128_bfloat16", 1000) == 57_012
+    assert lb("llama3_8b_64_bfloat16", 240) == 11_258_759
+    assert oracle.fsdp_lower_bound_us(3_752_999, 7_505_999, 32) == 11_141_695
+    assert oracle.fsdp_lower_bound_us(8_131_499, 16_262_998, 80) == 24_292_757
+
+
+def test_every_model_stats_table_parses(oracle):
+    d = os.path.join(ROOT, "model_stats")
+    files = sorted(f for f in os.listdir(d) if f.endswith(".txt"))
+    assert len(files) == 72
+    for f in files:
+        st = oracle.parse_model_stats(os.path.join(d, f))
+        assert st["modelSize"] > 0 and st["avgBackwardTime"] >= st["avgForwardTime"] > 0 and st["batchSize"] > 0
+
+
+def test_checksum_detects_permutation(oracle):
+    x = oracle.fill_pattern(1001, 0, 2, 1, 0)
+    y = x.copy()
+    y[[3, 4]] = y[[4, 3]]
+    assert oracle.checksum(x) != oracle.checksum(y)
+    assert oracle.checksum(x) == oracle.checksum(x.copy())
