@@ -87,6 +87,7 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_launch_count": (u64, []),
         "dlnb_iter_begin": (i, []),
         "dlnb_iter_end": (i, [C.POINTER(C.c_float)]),
+        "dlnb_batch_begin": (i, []),
         "dlnb_slot_elapsed": (i, [vp, i, C.POINTER(C.c_float)]),
         "dlnb_memcpy_h2d": (i, [vp, vp, sz]),
         "dlnb_memcpy_d2h": (i, [vp, vp, sz]),
@@ -242,6 +243,14 @@ def spin_calibrate() -> tuple[float, float]:
 
 def iter_begin() -> None:
     check(lib().dlnb_iter_begin())
+
+
+def batch_begin() -> None:
+    check(lib().dlnb_batch_begin())
+
+
+def set_option(key: str, value: int) -> None:
+    check(lib().dlnb_set(key.encode(), value))
 
 
 def iter_end() -> float:

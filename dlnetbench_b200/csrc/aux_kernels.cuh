@@ -7,16 +7,26 @@ namespace dlnb {
 
 // ----------------------------------------------------------------------------
 // Emulated compute: spin on %globaltimer for `ns` nanoseconds.
-// ----------------------------------------------------------------------------
-__global__ void spin_kernel(unsigned long long ns) {
+//// ----------------------------------------------------------------------------
+// Consecutive spins form one seamless stretch of "compute": a spin that starts within
+// `slack_ns` of the previous spin's NOMINAL end counts from that end, so launch gaps and
+// per-kernel timer granularity do not accumulate over a chain (a dp iteration is up to 4001
+// spins). stamps[parity] receives this spin's nominal end; stamps[parity ^ 1] holds the
+// previous one's (two words, so a late CTA never reads a stamp written by its own kernel).
+__global__ void spin_kernel(unsigned long long ns, unsigned long long *stamps, unsigned parity,
+                            unsigned long long slack_ns) {
     const unsigned long long t0 = globaltimer_ns();
+    const unsigned long long prev = stamps[parity ^ 1u];
+    const unsigned long long start = (t0 >= prev && t0 - prev <= slack_ns) ? prev : t0;
+    const unsigned long long deadline = start + ns;
     for (;;) {
-        const unsigned long long el = globaltimer_ns() - t0;
-        if (el >= ns) break;
-        const unsigned long long left = ns - el;
+        const unsigned long long now = globaltimer_ns();
+        if (now >= deadline) break;
+        const unsigned long long left = deadline - now;
         // back off while far from the deadline so the SM's issue slots stay free
         if (left > 4000) __nanosleep(left > 64000 ? 16000 : (unsigned)(left >> 2));
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) stamps[parity] = deadline;
 }
 
 // ----------------------------------------------------------------------------

@@ -23,12 +23,13 @@ constexpr int MAXR = 8;            // ranks of one NVSwitch box
 constexpr int MAX_FLAG_CTAS = 512; // flag rows per communicator
 constexpr int FLAG_ROW = 8;        // uint32 flags per row (one per source rank)
 
-// Per-communicator control block, local to each (virtual) rank.
+// Per-communicator control block, local to each (virtual) rank: one barrier generation per
+// CTA row (monotonic, wraps). Row b advances by 2 in every launch whose grid contains CTA b;
+// all ranks of a communicator launch the same grid for the same call, so row b holds the same
+// value on every rank. Kept in device memory (not a kernel argument) so a captured launch
+// replays correctly.
 struct CommCtl {
-    uint32_t epoch;   // last completed barrier generation (monotonic, wraps)
-    uint32_t done;    // CTAs that finished the current kernel
-    uint32_t error;   // 1 = watchdog fired
-    uint32_t pad;
+    uint32_t epoch[MAX_FLAG_CTAS];
 };
 
 // What one rank sees of a collective: its own and its peers' buffers and flags.
@@ -79,6 +80,14 @@ __device__ __forceinline__ void st_v4(uint4 *p, const uint4 &v) {
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
                  "r"(v.y), "r"(v.z), "r"(v.w)
                  : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
 __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -178,28 +187,38 @@ template <> struct Acc<__nv_bfloat16> {
 
 // ----------------------------------------------------------------------------
 // cross-GPU barrier between the CTAs of equal index on every rank.
-//   `gen` is the generation to reach. Flags are monotonic (never reset) and
-//   compared with wrap-safe >=, so a rank that runs ahead by one barrier is fine.
-//   Protocol: every thread's prior global/peer writes are ordered before the
-//   __syncthreads; thread p (<n) then fences at system scope and releases
-//   flag[peer p][cta][me] = gen, then acquires flag[me][cta][p] >= gen.
+//   `gen` is the generation to reach. Flags are monotonic (never reset) and compared with
+//   wrap-safe >=, so a rank that runs ahead by one barrier is fine.
+//   After a __syncthreads, thread p (< n) writes flag[peer p][cta][me] = gen and polls
+//   flag[me][cta][p] >= gen.
+//   PUBLISH = true  : this CTA wrote into peer memory before the barrier. The flag is stored
+//                     with release and read with acquire at system scope, so those writes are
+//                     visible to whoever passes the barrier (costs a wait for the write acks).
+//   PUBLISH = false : only reads happened (or nothing yet): relaxed flag traffic, no fence.
+//                     What peers read after it was produced by kernels that had completed
+//                     before the peer's kernel could write its flag.
 // ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cta_epoch(const RankView &v, int cta) {
+    return v.nranks > 1 ? *(volatile uint32_t *)&v.ctl->epoch[cta] : 0u;
+}
+
+template <bool PUBLISH>
 __device__ __forceinline__ void cta_barrier(const RankView &v, uint32_t gen, int cta) {
     if (v.nranks <= 1) return;
     __syncthreads();
     if (threadIdx.x < (unsigned)v.nranks) {
         const int p = threadIdx.x;
-        __threadfence_system();
-        st_release_sys(v.flags[p] + (size_t)cta * FLAG_ROW + v.rank, gen);
+        uint32_t *theirs = v.flags[p] + (size_t)cta * FLAG_ROW + v.rank;
         const uint32_t *mine = v.flags[v.rank] + (size_t)cta * FLAG_ROW + p;
+        if (PUBLISH) st_release_sys(theirs, gen);
+        else st_relaxed_sys(theirs, gen);
         unsigned long long t0 = 0;
         unsigned polls = 0;
-        while ((int32_t)(ld_acquire_sys(mine) - gen) < 0) {
+        while ((int32_t)((PUBLISH ? ld_acquire_sys(mine) : ld_relaxed_sys(mine)) - gen) < 0) {
             if ((++polls & 0x3ff) == 0) {
                 unsigned long long now = globaltimer_ns();
                 if (t0 == 0) t0 = now;
                 else if (now - t0 > v.timeout_ns) {
-                    v.ctl->error = 1;
                     if (v.host_error) *(volatile uint32_t *)v.host_error = 1;
                     __threadfence_system();
                     break;
@@ -210,18 +229,9 @@ __device__ __forceinline__ void cta_barrier(const RankView &v, uint32_t gen, int
     __syncthreads();
 }
 
-// The last CTA of a (virtual) rank to finish publishes the new generation.
-__device__ __forceinline__ void cta_finish(const RankView &v, uint32_t new_epoch, int nctas) {
-    if (v.nranks <= 1) return;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        if (atomicAdd(&v.ctl->done, 1u) == (unsigned)nctas - 1) {
-            v.ctl->done = 0;
-            v.ctl->epoch = new_epoch;
-            __threadfence();
-        }
-    }
+// Row `cta` has passed both barriers of this launch.
+__device__ __forceinline__ void cta_finish(const RankView &v, uint32_t new_epoch, int cta) {
+    if (v.nranks > 1 && threadIdx.x == 0) v.ctl->epoch[cta] = new_epoch;
 }
 
 // ----------------------------------------------------------------------------
@@ -239,11 +249,16 @@ __device__ __forceinline__ void reduce_store_vec(const uint4 *const *src, uint4 
 #pragma unroll
     for (int q = 0; q < NDST; ++q) d[q] = dst[q];
 
-    for (size_t base = tid; base < nvec; base += (size_t)U * nthr) {
+    // Tiled: a CTA streams contiguous tiles of U*blockDim.x vectors (tile index strides by the
+    // grid), a warp touches 512 contiguous bytes per load instruction.
+    const size_t bdim = blockDim.x, tile = (size_t)U * bdim;
+    const size_t cta = tid / bdim, nctas = nthr / bdim;
+    for (size_t t = cta; t * tile < nvec; t += nctas) {
+        const size_t base = t * tile + threadIdx.x;
         uint4 val[U][NSRC];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const size_t i = base + (size_t)u * nthr;
+            const size_t i = base + (size_t)u * bdim;
             if (i < nvec) {
 #pragma unroll
                 for (int p = 0; p < NSRC; ++p) val[u][p] = RO ? ld_v4_ro(s[p] + i) : ld_v4(s[p] + i);
@@ -251,7 +266,7 @@ __device__ __forceinline__ void reduce_store_vec(const uint4 *const *src, uint4 
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const size_t i = base + (size_t)u * nthr;
+            const size_t i = base + (size_t)u * bdim;
             if (i < nvec) {
                 uint4 out;
                 if (NSRC == 1) {
@@ -288,8 +303,10 @@ __device__ __forceinline__ void reduce_store_elem(const T *const *src, int nsrc,
 }
 
 template <int NR> struct Unroll {
-    // independent 128-bit loads in flight per thread ~ 16
-    static constexpr int U = NR >= 8 ? 2 : NR >= 4 ? 4 : NR >= 2 ? 8 : 8;
+    // U*NR independent 128-bit loads in flight per thread, at most 16 (64 data registers)
+    static constexpr int U = NR == 1 ? 4 : NR == 2 ? 8 : NR <= 4 ? 4 : 2;
+    // allgather: one local source, NR destinations (pointers, not data, fill the registers)
+    static constexpr int U_AG = NR <= 2 ? 4 : NR <= 4 ? 4 : 2;
 };
 
 __device__ __forceinline__ bool all_aligned16(const RankView &v, size_t send_off_bytes,
@@ -310,8 +327,8 @@ __device__ __forceinline__ bool all_aligned16(const RankView &v, size_t send_off
 template <typename T, int NR>
 __device__ __forceinline__ void allreduce_oneshot_body(const RankView &v, size_t count, int cta,
                                                        int nctas) {
-    const uint32_t e = v.ctl ? *(volatile uint32_t *)&v.ctl->epoch : 0;
-    cta_barrier(v, e + 1, cta);
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
 
     const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
     const size_t nthr = (size_t)nctas * blockDim.x;
@@ -323,7 +340,7 @@ __device__ __forceinline__ void allreduce_oneshot_body(const RankView &v, size_t
 #pragma unroll
         for (int p = 0; p < NR; ++p) src[p] = (const uint4 *)v.send[p];
         uint4 *dst[1] = {(uint4 *)mine};
-        reduce_store_vec<T, NR, 1, Unroll<NR>::U, false>(src, dst, nvec, tid, nthr);
+        reduce_store_vec<T, NR, 1, Unroll<NR>::U, NR == 1>(src, dst, nvec, tid, nthr);
         const size_t done = nvec * PV;
         if (done < count && cta == 0) {
             const T *ts[MAXR];
@@ -338,8 +355,8 @@ __device__ __forceinline__ void allreduce_oneshot_body(const RankView &v, size_t
         reduce_store_elem<T>(ts, NR, td, 1, count, tid, nthr);
     }
 
-    cta_barrier(v, e + 2, cta);
-    cta_finish(v, e + 2, nctas);
+    cta_barrier<false>(v, e + 2, cta); // only reads happened
+    cta_finish(v, e + 2, cta);
 }
 
 // ----------------------------------------------------------------------------
@@ -350,8 +367,8 @@ __device__ __forceinline__ void allreduce_oneshot_body(const RankView &v, size_t
 template <typename T, int NR>
 __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t count, int cta,
                                                        int nctas) {
-    const uint32_t e = v.ctl ? *(volatile uint32_t *)&v.ctl->epoch : 0;
-    cta_barrier(v, e + 1, cta);
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
 
     const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
     const size_t nthr = (size_t)nctas * blockDim.x;
@@ -368,7 +385,7 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
             src[p] = (const uint4 *)v.send[p] + v0;
             dst[p] = (uint4 *)v.recv[p] + v0;
         }
-        reduce_store_vec<T, NR, NR, Unroll<NR>::U, false>(src, dst, v1 - v0, tid, nthr);
+        reduce_store_vec<T, NR, NR, Unroll<NR>::U, NR == 1>(src, dst, v1 - v0, tid, nthr);
         // sub-vector tail (< 16 bytes): every rank reduces it for itself
         const size_t done = nvec * PV;
         if (done < count && cta == 0) {
@@ -390,8 +407,8 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
         reduce_store_elem<T>(ts, NR, td, NR, e1 - e0, tid, nthr);
     }
 
-    cta_barrier(v, e + 2, cta);
-    cta_finish(v, e + 2, nctas);
+    cta_barrier<true>(v, e + 2, cta); // publishes the pushed slices
+    cta_finish(v, e + 2, cta);
 }
 
 // ----------------------------------------------------------------------------
@@ -401,8 +418,8 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
 template <typename T, int NR>
 __device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcount, int cta,
                                                int nctas) {
-    const uint32_t e = v.ctl ? *(volatile uint32_t *)&v.ctl->epoch : 0;
-    cta_barrier(v, e + 1, cta);
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
 
     const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
     const size_t nthr = (size_t)nctas * blockDim.x;
@@ -417,7 +434,7 @@ __device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcou
         uint4 *dst[NR];
 #pragma unroll
         for (int p = 0; p < NR; ++p) dst[p] = (uint4 *)((T *)v.recv[p] + off);
-        reduce_store_vec<T, 1, NR, 8, true>(src, dst, nvec, tid, nthr);
+        reduce_store_vec<T, 1, NR, Unroll<NR>::U_AG, true>(src, dst, nvec, tid, nthr);
         const size_t done = nvec * PV;
         if (done < sendcount && cta == 0) {
             const T *ts[1] = {s + done};
@@ -432,8 +449,8 @@ __device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcou
         reduce_store_elem<T>(ts, 1, td, NR, sendcount, tid, nthr);
     }
 
-    cta_barrier(v, e + 2, cta);
-    cta_finish(v, e + 2, nctas);
+    cta_barrier<true>(v, e + 2, cta); // publishes the pushed shard
+    cta_finish(v, e + 2, cta);
 }
 
 // ----------------------------------------------------------------------------
@@ -444,8 +461,8 @@ __device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcou
 template <typename T, int NR>
 __device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t recvcount, int cta,
                                                     int nctas) {
-    const uint32_t e = v.ctl ? *(volatile uint32_t *)&v.ctl->epoch : 0;
-    cta_barrier(v, e + 1, cta);
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
 
     const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
     const size_t nthr = (size_t)nctas * blockDim.x;
@@ -460,7 +477,7 @@ __device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t re
 #pragma unroll
         for (int p = 0; p < NR; ++p) src[p] = (const uint4 *)((const T *)v.send[p] + off);
         uint4 *dst[1] = {(uint4 *)mine};
-        reduce_store_vec<T, NR, 1, Unroll<NR>::U, false>(src, dst, nvec, tid, nthr);
+        reduce_store_vec<T, NR, 1, Unroll<NR>::U, NR == 1>(src, dst, nvec, tid, nthr);
         const size_t done = nvec * PV;
         if (done < recvcount && cta == 0) {
             const T *ts[MAXR];
@@ -475,8 +492,8 @@ __device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t re
         reduce_store_elem<T>(ts, NR, td, 1, recvcount, tid, nthr);
     }
 
-    cta_barrier(v, e + 2, cta);
-    cta_finish(v, e + 2, nctas);
+    cta_barrier<false>(v, e + 2, cta); // only reads happened
+    cta_finish(v, e + 2, cta);
 }
 
 // ----------------------------------------------------------------------------
@@ -493,12 +510,20 @@ __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta,
     else reduce_scatter_body<T, NR>(v, count, cta, nctas);
 }
 
-// One kernel form for both modes: the views travel as a __grid_constant__ kernel
-// parameter (constant bank, no dependent global load on the latency path);
-// real mode fills v[0] only and launches gridDim.y == 1.
+// The rank's view travels as a __grid_constant__ kernel parameter (constant bank: no dependent
+// global load on the latency path). Real mode: one view, gridDim.y == 1. Emulation mode: one
+// view per virtual rank, gridDim.y == nranks, cooperative launch.
+// NR == 1 keeps <= 64 registers so two CTAs share an SM (the world-1 HBM copy wants the
+// occupancy), larger groups hold U*NR vectors in flight.
 template <typename T, int NR, int OP>
-__global__ void __launch_bounds__(512, 1)
-coll_kernel(const __grid_constant__ EmuViews ev, size_t count) {
+__global__ void __launch_bounds__(512, (NR == 1 ? 2 : 1))
+coll_kernel(const __grid_constant__ RankView v, size_t count) {
+    run_op<T, NR, OP>(v, count, blockIdx.x, gridDim.x);
+}
+
+template <typename T, int NR, int OP>
+__global__ void __launch_bounds__(512, (NR == 1 ? 2 : 1))
+coll_kernel_emu(const __grid_constant__ EmuViews ev, size_t count) {
     run_op<T, NR, OP>(ev.v[blockIdx.y], count, blockIdx.x, gridDim.x);
 }
 

@@ -120,7 +120,9 @@ struct Chunk {
 struct dlnb_comm {
     int id = 0, n = 1, me = 0, dtype = DLNB_F32, num_slots = 1;
     int ranks[MAXR] = {};
-    std::vector<cudaEvent_t> ev_start, ev_end;
+    std::vector<cudaEvent_t> ev_start, ev_end; // timing pair, recorded when slot_timing is on
+    std::vector<cudaEvent_t> ev_done;          // completion (no timestamp: cheaper), always recorded
+    std::vector<char> slot_timed;
     std::vector<char> slot_used;
     long ctas = 0, threads = 512, algo = DLNB_ALGO_AUTO, twoshot_min_bytes = 256 * 1024, timeout_ms = 30000;
 };
@@ -153,7 +155,9 @@ struct State {
     CommCtl *emu_ctl = nullptr;
     int emu_last_n = 0;
     // spin
-    long spin_ctas = 1, spin_threads = 32, slot_timing = 1;
+    long spin_ctas = 1, spin_threads = 32, slot_timing = 1, spin_slack_ns = 4000;
+    unsigned long long *spin_stamps = nullptr;
+    unsigned spin_seq = 0;
     double spin_overhead_us = 0.0, spin_slope = 1.0;
     // misc
     uint64_t launches = 0;
@@ -352,6 +356,8 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     *G.host_error = 0;
     CU_TRY(cudaHostGetDevicePointer((void **)&G.host_error_dev, G.host_error, 0));
     CU_TRY(cudaMalloc((void **)&G.d_scalar, sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc((void **)&G.spin_stamps, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(G.spin_stamps, 0, 2 * sizeof(unsigned long long)));
 
     G.inited = true;
     // first symmetric allocations: flag rows and control blocks of all communicators
@@ -371,6 +377,7 @@ extern "C" int dlnb_finalize(void) {
         if (!c) continue;
         for (auto e : c->ev_start) cudaEventDestroy(e);
         for (auto e : c->ev_end) cudaEventDestroy(e);
+        for (auto e : c->ev_done) cudaEventDestroy(e);
         delete c;
     }
     G.comms.clear();
@@ -398,6 +405,7 @@ extern "C" int dlnb_finalize(void) {
     if (G.emu_ctl) cudaFree(G.emu_ctl);
     if (G.flush_buf) cudaFree(G.flush_buf);
     if (G.d_scalar) cudaFree(G.d_scalar);
+    if (G.spin_stamps) cudaFree(G.spin_stamps);
     if (G.host_error) cudaFreeHost(G.host_error);
     cudaStreamDestroy(G.s_compute);
     cudaStreamDestroy(G.s_comm);
@@ -435,6 +443,7 @@ extern "C" int dlnb_set(const char *key, long value) {
     if (!strcmp(key, "spin_ctas")) G.spin_ctas = std::max(1L, value);
     else if (!strcmp(key, "spin_threads")) G.spin_threads = std::min(1024L, std::max(1L, value));
     else if (!strcmp(key, "slot_timing")) G.slot_timing = value;
+    else if (!strcmp(key, "spin_slack_ns")) G.spin_slack_ns = std::max(0L, value);
     else return fail("dlnb_set: unknown key %s", key);
     return 0;
 }
@@ -442,6 +451,7 @@ extern "C" long dlnb_get(const char *key) {
     if (!strcmp(key, "spin_ctas")) return G.spin_ctas;
     if (!strcmp(key, "spin_threads")) return G.spin_threads;
     if (!strcmp(key, "slot_timing")) return G.slot_timing;
+    if (!strcmp(key, "spin_slack_ns")) return G.spin_slack_ns;
     if (!strcmp(key, "sms")) return G.sms;
     return -1;
 }
@@ -476,10 +486,13 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
     // one extra, internal slot (index num_slots) for the blocking calls
     c->ev_start.resize(c->num_slots + 1);
     c->ev_end.resize(c->num_slots + 1);
+    c->ev_done.resize(c->num_slots + 1);
+    c->slot_timed.assign(c->num_slots + 1, 0);
     c->slot_used.assign(c->num_slots + 1, 0);
     for (int i = 0; i <= c->num_slots; ++i) {
         CU_TRY(cudaEventCreate(&c->ev_start[i]));
         CU_TRY(cudaEventCreate(&c->ev_end[i]));
+        CU_TRY(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
     }
     if (const char *v = getenv("DLNB_CTAS")) c->ctas = atol(v);
     if (const char *v = getenv("DLNB_THREADS")) c->threads = atol(v);
@@ -495,6 +508,7 @@ extern "C" int dlnb_comm_destroy(dlnb_comm_t c) {
         if (slot == c) slot = nullptr;
     for (auto e : c->ev_start) cudaEventDestroy(e);
     for (auto e : c->ev_end) cudaEventDestroy(e);
+    for (auto e : c->ev_done) cudaEventDestroy(e);
     delete c;
     return 0;
 }
@@ -524,17 +538,20 @@ extern "C" long dlnb_comm_get(dlnb_comm_t c, const char *key) {
 // ---------------------------------------------------------------------------
 // emulated compute
 // ---------------------------------------------------------------------------
-extern "C" int dlnb_compute_spin(double usec) {
-    NEED_INIT();
-    if (!(usec > 0)) return 0;
-    double req = (usec - G.spin_overhead_us) / G.spin_slope;
-    if (req < 0) req = 0;
+static int launch_spin(double ns) {
     spin_kernel<<<(unsigned)G.spin_ctas, (unsigned)G.spin_threads, 0, G.s_compute>>>(
-        (unsigned long long)(req * 1000.0 + 0.5));
+        (unsigned long long)(ns + 0.5), G.spin_stamps, G.spin_seq++ & 1u, (unsigned long long)G.spin_slack_ns);
     CU_TRY(cudaGetLastError());
     G.launches++;
     G.compute_dirty = true;
     return 0;
+}
+extern "C" int dlnb_compute_spin(double usec) {
+    NEED_INIT();
+    if (!(usec > 0)) return 0;
+    // only the clock-rate correction is applied: the start-up latency of the first spin of a
+    // chain is genuine emulation overhead and stays in the measurement
+    return launch_spin(usec * 1000.0 / G.spin_slope);
 }
 extern "C" int dlnb_compute_sync(void) {
     NEED_INIT();
@@ -543,35 +560,29 @@ extern "C" int dlnb_compute_sync(void) {
 }
 extern "C" int dlnb_spin_calibrate(double *overhead_us, double *slope) {
     NEED_INIT();
-    // K back-to-back spins of `req` us each between two events: per-spin cost
-    // includes the kernel-to-kernel gap, which is what the proxies see.
-    const double reqs[3] = {20.0, 200.0, 1000.0};
-    double got[3];
-    const int K = 16;
+    // Two isolated spins, device-timed with events: achieved = overhead + slope * requested.
+    // slope is the ratio between the event clock and %globaltimer (measured ~1.0006 on B200);
+    // overhead is the launch-to-first-instruction latency of an isolated spin (reported only).
+    const double reqs[2] = {200.0, 20000.0};
+    double got[2];
     CU_TRY(cudaStreamSynchronize(G.s_compute));
-    for (int i = 0; i < 3; ++i) {
+    for (int i = 0; i < 2; ++i) {
         double best = 1e30;
-        for (int rep = 0; rep < 3; ++rep) {
+        for (int rep = 0; rep < 4; ++rep) {
             CU_TRY(cudaEventRecord(G.ev_tmp0, G.s_compute));
-            for (int k = 0; k < K; ++k) {
-                spin_kernel<<<(unsigned)G.spin_ctas, (unsigned)G.spin_threads, 0, G.s_compute>>>(
-                    (unsigned long long)(reqs[i] * 1000.0));
-                G.launches++;
-            }
+            if (launch_spin(reqs[i] * 1000.0)) return 1;
             CU_TRY(cudaEventRecord(G.ev_tmp1, G.s_compute));
             CU_TRY(cudaEventSynchronize(G.ev_tmp1));
             float ms = 0;
             CU_TRY(cudaEventElapsedTime(&ms, G.ev_tmp0, G.ev_tmp1));
-            best = std::min(best, (double)ms * 1000.0 / K);
+            best = std::min(best, (double)ms * 1000.0);
+            usleep(50); // break the chain: the next spin must start from its own clock
         }
         got[i] = best;
     }
-    // least squares through the three points
-    double sx = 0, sy = 0, sxx = 0, sxy = 0;
-    for (int i = 0; i < 3; ++i) { sx += reqs[i]; sy += got[i]; sxx += reqs[i] * reqs[i]; sxy += reqs[i] * got[i]; }
-    double b = (3 * sxy - sx * sy) / (3 * sxx - sx * sx);
-    double a = (sy - b * sx) / 3;
-    if (!(b > 0.5 && b < 2.0)) { a = 0; b = 1; }
+    double b = (got[1] - got[0]) / (reqs[1] - reqs[0]);
+    double a = got[0] - b * reqs[0];
+    if (!(b > 0.9 && b < 1.1)) { a = 0; b = 1; }
     if (a < 0) a = 0;
     G.spin_overhead_us = a;
     G.spin_slope = b;
@@ -614,12 +625,14 @@ static size_t work_bytes(int op, int n, size_t count, size_t esz) {
 static int pick_grid(long want, int dtype, int op, int n, int threads, size_t bytes, int *out) {
     int occ = occupancy_dtype(dtype, op, n, threads);
     if (occ <= 0) return fail("collective kernel does not fit on an SM with %d threads", threads);
-    int cap = std::min(G.sms * occ, MAX_FLAG_CTAS);
+    // n > 1: every CTA waits on its peers' CTA of the same index, so all must be resident;
+    // n == 1: no barriers, and 4 CTAs per SM (two waves at occupancy 2) measured best for HBM
+    int cap = n == 1 ? G.sms * 16 : std::min(G.sms * occ, MAX_FLAG_CTAS);
     long g;
     if (want > 0) {
         g = want;
     } else if (n == 1) {
-        g = (long)G.sms * occ; // pure HBM copy: fill the machine
+        g = (long)G.sms * 4;
     } else {
         g = 64; // NVLink-bound: enough bytes in flight without taking every SM
     }
@@ -687,7 +700,9 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
         if (e != cudaSuccess) return fail("collective launch failed: %s", cudaGetErrorString(e));
         G.launches++;
     }
-    CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+    if (G.slot_timing) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+    CU_TRY(cudaEventRecord(c->ev_done[slot], G.s_comm));
+    c->slot_timed[slot] = G.slot_timing ? 1 : 0;
     c->slot_used[slot] = 1;
     return 0;
 }
@@ -715,7 +730,7 @@ extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
     if (slot == -1) slot = c->num_slots;
     else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
     if (!c->slot_used[slot]) return 0;
-    CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
+    CU_TRY(cudaEventSynchronize(c->ev_done[slot]));
     return check_watchdog();
 }
 extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
@@ -725,7 +740,7 @@ extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
     // the communication stream is ordered: waiting for the newest used slot suffices,
     // but slots may have been recorded in any order, so wait for each.
     for (int i = 0; i < nslots; ++i)
-        if (c->slot_used[i]) CU_TRY(cudaEventSynchronize(c->ev_end[i]));
+        if (c->slot_used[i]) CU_TRY(cudaEventSynchronize(c->ev_done[i]));
     return check_watchdog();
 }
 extern "C" int dlnb_barrier(dlnb_comm_t c) {
@@ -751,6 +766,7 @@ extern "C" int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms) {
     if (!c || !ms) return fail("null argument");
     if (slot == -1) slot = c->num_slots; // the most recent blocking call
     if (slot < 0 || slot > c->num_slots || !c->slot_used[slot]) return fail("slot %d has no recorded collective", slot);
+    if (!c->slot_timed[slot]) return fail("slot %d was recorded with slot_timing off", slot);
     CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
     CU_TRY(cudaEventElapsedTime(ms, c->ev_start[slot], c->ev_end[slot]));
     return 0;
@@ -767,6 +783,17 @@ extern "C" int dlnb_iter_begin(void) {
     CU_TRY(cudaEventRecord(G.ev_iter0, G.s_compute));
     CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_iter0, 0));
     CU_TRY(cudaStreamWaitEvent(G.s_copy, G.ev_iter0, 0));
+    return 0;
+}
+extern "C" int dlnb_batch_begin(void) {
+    NEED_INIT();
+    // starts the device timer ON THE COMMUNICATION STREAM, behind everything enqueued so far on
+    // any stream: with a long spin enqueued first, the host can queue a whole batch of
+    // collectives before the first one runs, and dlnb_iter_end() then reads pure device time.
+    G.compute_dirty = true;
+    G.copy_dirty = true;
+    if (join_streams()) return 1;
+    CU_TRY(cudaEventRecord(G.ev_iter0, G.s_comm));
     return 0;
 }
 extern "C" int dlnb_iter_end(float *ms) {

@@ -98,10 +98,15 @@ long dlnb_comm_get(dlnb_comm_t c, const char *key);
  * calibrated %globaltimer spin kernel on the compute stream. Asynchronous. */
 int dlnb_compute_spin(double usec);
 int dlnb_compute_sync(void);
-/* Measures requested→achieved duration of the spin kernel and stores the linear
- * correction; returns fixed overhead (us) and slope through the out-params. */
+/* Consecutive spins chain: one that starts within "spin_slack_ns" (default 4000) of the
+ * previous spin's nominal end counts from that end, so a chain of k spins lasts the sum of
+ * the requests, not k launch gaps more.
+ * dlnb_spin_calibrate measures two isolated spins with CUDA events: `slope` = event clock vs
+ * %globaltimer rate (applied to every request), `overhead_us` = start-up latency of an
+ * isolated spin (reported, not subtracted). */
 int dlnb_spin_calibrate(double *overhead_us, double *slope);
-/* "spin_ctas": CTAs of the spin kernel (SM footprint of the emulated compute). */
+/* "spin_ctas" / "spin_threads": footprint of the spin kernel (SM share of the emulated
+ * compute); "spin_slack_ns": chaining window; "slot_timing": record a start event per slot. */
 int dlnb_set(const char *key, long value);
 long dlnb_get(const char *key);
 
@@ -134,6 +139,10 @@ uint64_t dlnb_launch_count(void);
  * ccutils CCUTILS_MPI_TIMER_*): cudaEvent pair spanning both streams. */
 int dlnb_iter_begin(void);
 int dlnb_iter_end(float *ms);
+/* like dlnb_iter_begin, but the timer starts on the communication stream behind everything
+ * enqueued so far (e.g. a long spin): times a pre-queued batch of collectives on the device
+ * with the host out of the loop. Stop with dlnb_iter_end(). */
+int dlnb_batch_begin(void);
 /* device time of the most recent collective recorded in `slot` (ms); slot -1 = the most
  * recent BLOCKING call (those use an internal slot, never one of the caller's) */
 int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms);

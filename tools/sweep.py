@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--algo", type=int, default=0)
     ap.add_argument("--threads", type=int, default=512)
     ap.add_argument("--out", default="")
+    ap.add_argument("--per-slot", dest="b2b", action="store_false", help="busBW from per-launch slot events instead of the back-to-back batch")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", os.environ.get("DLNB_RANK", 0)))
     world = int(os.environ.get("WORLD_SIZE", os.environ.get("DLNB_WORLD", 1)))
@@ -63,7 +64,22 @@ def main():
                         capi.check(capi.lib().dlnb_ireduce_scatter(comm.h, s.data, r.data, rc, i))
                 comm.WaitAll(a.iters)
             ms = sorted(comm.slot_ms(i) for i in range(a.iters))
-            med = ms[len(ms) // 2]
+            # device-only batch time: a spin blocks the communication stream while the host queues
+            # the whole batch (no per-slot timing events), one event pair around the batch
+            capi.set_option("slot_timing", 0)
+            capi.compute_spin(max(3000.0, 40.0 * a.iters))
+            capi.batch_begin()
+            for i in range(a.iters):
+                s, r = send[i % nbuf], recv[i % nbuf]
+                if a.op == "allreduce":
+                    comm.Iallreduce(s.data, r.data, sc, i)
+                elif a.op == "allgather":
+                    comm.Iallgather(s.data, sc, r.data, sc, i)
+                else:
+                    capi.check(capi.lib().dlnb_ireduce_scatter(comm.h, s.data, r.data, rc, i))
+            b2b = capi.iter_end() / a.iters
+            capi.set_option("slot_timing", 1)
+            med = b2b if a.b2b else ms[len(ms) // 2]
             if world == 1:
                 bus = 2 * sc * esz / (med * 1e-3) / 1e9
             elif a.op == "allreduce":
@@ -71,7 +87,7 @@ def main():
             else:
                 bus = (world - 1) / world * max(sc, rc) * esz / (med * 1e-3) / 1e9
             row = dict(op=a.op, dtype=a.dtype, world=world, bytes=sc * esz if a.op != "reduce_scatter" else sc * esz,
-                       ctas=ctas, us_med=med * 1e3, us_min=ms[0] * 1e3, busbw_GBps=bus)
+                       ctas=ctas, us=med * 1e3, us_slot_med=ms[len(ms) // 2] * 1e3, us_b2b=b2b * 1e3, busbw_GBps=bus)
             rows.append(row)
             if rank == 0:
                 print(json.dumps(row), flush=True)
