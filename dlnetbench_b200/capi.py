@@ -102,6 +102,7 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_emu_allreduce": (i, [i, pvp, pvp, sz, i, i, i]),
         "dlnb_emu_allgather": (i, [i, pvp, pvp, sz, i, i]),
         "dlnb_emu_reduce_scatter": (i, [i, pvp, pvp, sz, i, i]),
+        "dlnb_emu_allreduce_noalloc": (i, [i, pvp, pvp, sz, i, i, i]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -272,6 +273,11 @@ def _ptr_array(ptrs):
 
 def emu_allreduce(send_ptrs, recv_ptrs, count, dtype, algo=ALGO_AUTO, ctas=0):
     check(lib().dlnb_emu_allreduce(len(send_ptrs), _ptr_array(send_ptrs), _ptr_array(recv_ptrs), count, dtype, algo, ctas))
+
+
+def emu_allreduce_noalloc(send_ptrs, recv_ptrs, count, dtype, algo=ALGO_AUTO, ctas=0):
+    """dlnb_emu_allreduce_noalloc: same result as emu_allreduce, scratch from the library image (<= 64 CTAs)."""
+    check(lib().dlnb_emu_allreduce_noalloc(len(send_ptrs), _ptr_array(send_ptrs), _ptr_array(recv_ptrs), count, dtype, algo, ctas))
 
 
 def emu_allgather(send_ptrs, recv_ptrs, sendcount, dtype, ctas=0):

@@ -986,3 +986,86 @@ extern "C" int dlnb_emu_reduce_scatter(int nranks, const void *const *send, void
                                        int dtype, int ctas) {
     return emu(OP_RS, nranks, send, recv, recvcount, dtype, ctas);
 }
+
+// ---------------------------------------------------------------------------
+// dlnb_emu_allreduce_noalloc — the emulated n-rank allreduce for callers that may not allocate
+// ---------------------------------------------------------------------------
+// Who this is for: a host program that has already handed every free byte of HBM to its own
+// pool (a framework's caching allocator, or a proxy run sized to fill the card), or one that is
+// in the middle of overlapped compute/communication where cudaMalloc's device-wide
+// synchronisation would stall the other streams. dlnb_emu_allreduce() above takes its flag rows
+// and per-row generations from cudaMalloc on first use; this variant takes them from a fixed
+// array that is part of the library image instead, so the call itself never asks the driver for
+// memory. The price is a hard upper bound on the launch shape and that all calls share the array.
+//
+//   scratch layout (18 KiB, resident on every GPU that loads the library, until exit):
+//     [0, 16 KiB)        flag rows   : 8 virtual ranks x 64 CTA rows x 8 source ranks x uint32
+//     [16 KiB, 18 KiB)   generations : 8 virtual ranks x 64 CTA rows x uint32
+#define DLNB_NOALLOC_MAX_CTAS 64
+#define DLNB_NOALLOC_FLAG_BYTES (MAXR * DLNB_NOALLOC_MAX_CTAS * FLAG_ROW * 4)
+#define DLNB_NOALLOC_EPOCH_BYTES (MAXR * DLNB_NOALLOC_MAX_CTAS * 4)
+static __device__ __align__(256) unsigned char dlnb_noalloc_scratch[DLNB_NOALLOC_FLAG_BYTES + DLNB_NOALLOC_EPOCH_BYTES];
+
+// In host code the name above is only a handle for the runtime, not a device address: the
+// address each device gave the array is looked up once per device and kept here.
+static unsigned char *g_noalloc_dev_ptr[64] = {};
+
+extern "C" int dlnb_emu_allreduce_noalloc(int nranks, const void *const *send, void *const *recv, size_t count,
+                                          int dtype, int algo, int ctas) {
+    NEED_INIT();
+    if (nranks < 1 || nranks > MAXR) return fail("emu_allreduce_noalloc: nranks %d not in 1..%d", nranks, MAXR);
+    if (!send || !recv) return fail("emu_allreduce_noalloc: null buffer list");
+    if (dtype < DLNB_F32 || dtype > DLNB_BF16) return fail("emu_allreduce_noalloc: unknown dtype %d", dtype);
+    if (ctas > DLNB_NOALLOC_MAX_CTAS)
+        return fail("emu_allreduce_noalloc: %d CTAs per virtual rank requested, the built-in scratch holds flag rows for "
+                    "at most %d (use dlnb_emu_allreduce for larger grids)", ctas, DLNB_NOALLOC_MAX_CTAS);
+    if (!count) return 0;
+
+    // set-up, once per device, with that device current
+    int dev = -1;
+    CU_TRY(cudaGetDevice(&dev));
+    if (dev != G.device) return fail("emu_allreduce_noalloc: device %d is current, the library was initialised on %d", dev, G.device);
+    if (dev < 0 || dev >= 64) return fail("emu_allreduce_noalloc: device index %d not supported", dev);
+    if (!g_noalloc_dev_ptr[dev]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, dlnb_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail("cudaGetSymbolAddress(dlnb_noalloc_scratch) failed: %s", cudaGetErrorString(e));
+        g_noalloc_dev_ptr[dev] = (unsigned char *)p;
+    }
+    unsigned char *scratch = g_noalloc_dev_ptr[dev];
+
+    // the array still holds the flags and generations of whatever call came last (maybe with another
+    // group size): every call starts all rows from generation 0
+    CU_TRY(cudaMemsetAsync(scratch, 0, DLNB_NOALLOC_FLAG_BYTES + DLNB_NOALLOC_EPOCH_BYTES, G.s_comm));
+
+    const int op = (algo == DLNB_ALGO_ONESHOT) ? OP_AR1 : (algo == DLNB_ALGO_TWOSHOT) ? OP_AR2
+                   : (count * dtype_size(dtype) < 256 * 1024 ? OP_AR1 : OP_AR2);
+    EmuViews ev;
+    memset(&ev, 0, sizeof(ev));
+    const size_t flags_per_rank = (size_t)DLNB_NOALLOC_MAX_CTAS * FLAG_ROW * 4;
+    for (int r = 0; r < nranks; ++r) {
+        RankView &v = ev.v[r];
+        v.rank = r;
+        v.nranks = nranks;
+        for (int p = 0; p < nranks; ++p) {
+            v.send[p] = send[p];
+            v.recv[p] = recv[p];
+            v.flags[p] = (uint32_t *)(scratch + (size_t)p * flags_per_rank);
+        }
+        // only rows < grid <= DLNB_NOALLOC_MAX_CTAS of the generation table are ever touched
+        v.ctl = (CommCtl *)(scratch + DLNB_NOALLOC_FLAG_BYTES + (size_t)r * DLNB_NOALLOC_MAX_CTAS * 4);
+        v.host_error = G.host_error_dev;
+        v.timeout_ns = 10ull * 1000000000ull;
+    }
+    const int threads = 512;
+    const int occ = occupancy_dtype(dtype, op, nranks, threads);
+    if (occ <= 0) return fail("emu_allreduce_noalloc: kernel does not fit");
+    const int cap = std::min((G.sms * occ) / nranks, DLNB_NOALLOC_MAX_CTAS); // all virtual ranks co-resident
+    const int grid = ctas > 0 ? std::min(ctas, cap) : std::min(16, cap);
+    if (grid < 1) return fail("emu_allreduce_noalloc: device too small for %d virtual ranks", nranks);
+    cudaError_t e = launch_dtype(dtype, op, nranks, dim3(grid, nranks, 1), threads, G.s_comm, ev, count, true);
+    if (e != cudaSuccess) return fail("emu_allreduce_noalloc launch failed: %s", cudaGetErrorString(e));
+    G.launches++;
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    return check_watchdog();
+}

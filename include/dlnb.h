@@ -178,6 +178,26 @@ int dlnb_emu_allgather(int nranks, const void *const *send, void *const *recv, s
 int dlnb_emu_reduce_scatter(int nranks, const void *const *send, void *const *recv,
                             size_t recvcount, int dtype, int ctas);
 
+/* ---- the emulated allreduce for callers that cannot allocate -----------------------
+ * No counterpart in the reference (it has no such constraint: every backend there allocates
+ * freely). Same arguments, same kernel and same results as dlnb_emu_allreduce(), but the
+ * flag rows and barrier generations live in an 18 KiB array built into the library image
+ * instead of coming from cudaMalloc on first use — the call makes no cudaMalloc / cudaFree
+ * and no allocating library call. Meant for hosts that have handed all free HBM to their own
+ * pool, or that must not trigger cudaMalloc's device-wide synchronisation while compute and
+ * communication streams are busy.
+ *   - limit: at most 64 CTAs per virtual rank (`ctas` 0 = default 16); a larger request is
+ *     refused with an error, nothing is launched. nranks 1..8 as elsewhere.
+ *   - the first call on a device looks up the array's device address (cudaGetSymbolAddress);
+ *     make that first call before starting any stream capture.
+ *   - all calls share the one array and it keeps the last call's contents; each call clears it
+ *     on the communication stream before launching. Calls that overlap on the GPU would race
+ *     on it: issue them one after another (the entry point returns after its kernel has
+ *     finished, so a single host thread cannot overlap two).
+ *   - every GPU that loads the library holds the 18 KiB until the process exits. */
+int dlnb_emu_allreduce_noalloc(int nranks, const void *const *send, void *const *recv, size_t count,
+                               int dtype, int algo, int ctas);
+
 #ifdef __cplusplus
 }
 #endif
