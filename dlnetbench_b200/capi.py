@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libdlnb.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "dlnb.h")
 
 F32, F16, BF16 = 0, 1, 2
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1, 2
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_MULTIMEM = 0, 1, 2, 3
 PAT_ZERO, PAT_INT, PAT_UNIFORM = 0, 1, 2
 DTYPE_SIZE = {F32: 4, F16: 2, BF16: 2}
 

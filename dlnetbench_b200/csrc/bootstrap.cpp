@@ -200,4 +200,17 @@ std::string Bootstrap::exchange_fds(int myfd, std::vector<int> &out) {
     return "";
 }
 
+std::string Bootstrap::bcast_fd(int root_fd, int &out) {
+    out = -1;
+    if (world_ <= 1 || rank_ == 0) {
+        out = ::dup(root_fd);
+        if (world_ > 1)
+            for (int r = 1; r < world_; ++r)
+                if (!send_fds(peers_[r], &root_fd, 1)) return "fd broadcast: send to a peer failed";
+        return "";
+    }
+    if (!recv_fds(peers_[0], &out, 1)) return "fd broadcast: receive from the hub failed";
+    return "";
+}
+
 } // namespace dlnb

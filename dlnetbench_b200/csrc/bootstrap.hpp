@@ -26,6 +26,8 @@ class Bootstrap {
     // every rank contributes one fd; every rank receives all `world` fds (its own
     // entry is a duplicate of what it sent). Caller closes them.
     std::string exchange_fds(int myfd, std::vector<int> &out);
+    // rank 0's fd reaches every rank (returned in `out`; rank 0 gets a duplicate). Caller closes it.
+    std::string bcast_fd(int root_fd, int &out);
 
   private:
     int rank_ = 0, world_ = 1;

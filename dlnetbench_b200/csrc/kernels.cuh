@@ -39,6 +39,8 @@ struct RankView {
     const void *send[MAXR];    // send[p]: rank p's send buffer (my mapping of it)
     void *recv[MAXR];          // recv[p]: rank p's recv buffer
     uint32_t *flags[MAXR];     // flags[p]: rank p's flag rows for this communicator
+    const void *mc_send;       // multicast address of the send buffer (all ranks' copies), or null
+    void *mc_recv;             // multicast address of the recv buffer, or null
     CommCtl *ctl;              // my control block
     uint32_t *host_error;      // mapped pinned word, set by the watchdog (may be null)
     unsigned long long timeout_ns;
@@ -285,7 +287,7 @@ __device__ __forceinline__ void reduce_store_vec(const uint4 *const *src, uint4 
     }
 }
 
-// Element-wise version for heads, tails and (for now) misaligned chunks.
+// Element-wise version for heads, tails and buffers with non-uniform alignment.
 template <typename T>
 __device__ __forceinline__ void reduce_store_elem(const T *const *src, int nsrc, T *const *dst,
                                                   int ndst, size_t n, size_t tid, size_t nthr) {
@@ -306,17 +308,173 @@ template <int NR> struct Unroll {
     // U*NR independent 128-bit loads in flight per thread, at most 16 (64 data registers)
     static constexpr int U = NR == 1 ? 4 : NR == 2 ? 8 : NR <= 4 ? 4 : 2;
     // allgather: one local source, NR destinations (pointers, not data, fill the registers)
-    static constexpr int U_AG = NR <= 2 ? 4 : NR <= 4 ? 4 : 2;
+    static constexpr int U_AG = NR <= 4 ? 4 : 2;
+    // shifted path keeps the neighbour's vector too
+    static constexpr int U_SH = NR <= 2 ? 4 : NR <= 4 ? 2 : 1;
 };
 
-__device__ __forceinline__ bool all_aligned16(const RankView &v, size_t send_off_bytes,
-                                              size_t recv_off_bytes) {
-    bool ok = true;
-    for (int p = 0; p < v.nranks; ++p) {
-        ok = ok && (((uintptr_t)v.send[p] + send_off_bytes) & 15) == 0;
-        ok = ok && (((uintptr_t)v.recv[p] + recv_off_bytes) & 15) == 0;
+// ----------------------------------------------------------------------------
+// Shifted data mover for chunks whose sources are NOT 16-byte aligned relative to their
+// (aligned) destinations — odd shard sizes put rank r's chunk at r*count*sizeof(T), e.g. the
+// 110,240,167-element fp16 shards of llama3_70b. All sources share the misalignment `m`
+// (0 < m < 16, a multiple of sizeof(T)); `src[p]` are the ALIGNED addresses just below the
+// data. Output vector j = bytes [m, m+16) of the pair (A[j], A[j+1]) where A[j] is the
+// rank-order fp32 sum of the sources' aligned vectors (the sum is element-wise, so summing
+// in the aligned frame and shifting afterwards gives the same bits). A thread gets A[j+1]
+// from its right-hand lane by shuffle; lane 31 loads it. Loads A[0..nvec], stores nvec vectors.
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ uint4 shift_pair(const uint4 &a, const uint4 &b, unsigned m) {
+    const unsigned mw = m >> 2, sh = (m & 3u) * 8u;
+    uint32_t w0, w1, w2, w3, w4;
+    switch (mw) {
+    case 0: w0 = a.x; w1 = a.y; w2 = a.z; w3 = a.w; w4 = b.x; break;
+    case 1: w0 = a.y; w1 = a.z; w2 = a.w; w3 = b.x; w4 = b.y; break;
+    case 2: w0 = a.z; w1 = a.w; w2 = b.x; w3 = b.y; w4 = b.z; break;
+    default: w0 = a.w; w1 = b.x; w2 = b.y; w3 = b.z; w4 = b.w; break;
     }
-    return ok;
+    return make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh),
+                      __funnelshift_r(w3, w4, sh));
+}
+
+template <typename T, int NSRC>
+__device__ __forceinline__ uint4 load_sum(const uint4 *const (&s)[NSRC], size_t i) {
+    uint4 val[NSRC];
+#pragma unroll
+    for (int p = 0; p < NSRC; ++p) val[p] = ld_v4(s[p] + i);
+    if (NSRC == 1) return val[0];
+    Acc<T> acc;
+    acc.set(val[0]);
+#pragma unroll
+    for (int p = 1; p < NSRC; ++p) acc.add(val[p]);
+    return acc.pack();
+}
+
+template <typename T, int NSRC, int NDST, int U>
+__device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src, uint4 *const *dst, size_t nvec,
+                                                         unsigned m, size_t tid, size_t nthr) {
+    const uint4 *s[NSRC];
+    uint4 *d[NDST];
+#pragma unroll
+    for (int p = 0; p < NSRC; ++p) s[p] = src[p];
+#pragma unroll
+    for (int q = 0; q < NDST; ++q) d[q] = dst[q];
+    const size_t bdim = blockDim.x, tile = (size_t)U * bdim;
+    const size_t cta = tid / bdim, nctas = nthr / bdim;
+    const unsigned lane = threadIdx.x & 31u;
+    // whole warps walk the loop together (the shuffle needs every lane)
+    for (size_t t = cta; t * tile < nvec; t += nctas) {
+        const size_t base = t * tile + threadIdx.x;
+        // Phase 1: raw loads only, no use of a loaded value inside any branch (a use would make
+        // the warp wait for that round trip before issuing the next loads). Indices are clamped
+        // to nvec (A[nvec] is always readable) instead of predicated. Lane 31 also fetches the
+        // vector its right-hand neighbour would hold.
+        uint4 val[U][NSRC], xv[U][NSRC];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = min(base + (size_t)u * bdim, nvec);
+#pragma unroll
+            for (int p = 0; p < NSRC; ++p) val[u][p] = ld_v4(s[p] + i);
+        }
+        if (lane == 31u) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t i = min(base + (size_t)u * bdim + 1, nvec);
+#pragma unroll
+                for (int p = 0; p < NSRC; ++p) xv[u][p] = ld_v4(s[p] + i);
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int p = 0; p < NSRC; ++p) xv[u][p] = make_uint4(0, 0, 0, 0);
+        }
+        // Phase 2: sums in rank order, neighbour exchange, shift, store
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = base + (size_t)u * bdim;
+            uint4 cur, ext;
+            if (NSRC == 1) {
+                cur = val[u][0];
+                ext = xv[u][0];
+            } else {
+                Acc<T> a, b;
+                a.set(val[u][0]);
+                b.set(xv[u][0]);
+#pragma unroll
+                for (int p = 1; p < NSRC; ++p) {
+                    a.add(val[u][p]);
+                    b.add(xv[u][p]);
+                }
+                cur = a.pack();
+                ext = b.pack();
+            }
+            uint4 nxt;
+            nxt.x = __shfl_down_sync(0xffffffffu, cur.x, 1);
+            nxt.y = __shfl_down_sync(0xffffffffu, cur.y, 1);
+            nxt.z = __shfl_down_sync(0xffffffffu, cur.z, 1);
+            nxt.w = __shfl_down_sync(0xffffffffu, cur.w, 1);
+            if (lane == 31u) nxt = ext;
+            if (i < nvec) {
+                const uint4 out = shift_pair(cur, nxt, m);
+#pragma unroll
+                for (int q = 0; q < NDST; ++q) st_v4(d[q] + i, out);
+            }
+        }
+    }
+}
+
+// ----------------------------------------------------------------------------
+// out[i] = sum_p src[p][i] for i in [0, count), stored to every dst[q] — any alignment.
+// Sources must share one alignment class and destinations another (true for every
+// collective here: all ranks use the same offsets into equally aligned buffers); otherwise
+// the element-wise path does the whole range. Head elements are peeled until the
+// destinations are 16-byte aligned, the bulk goes through the aligned or the shifted
+// 128-bit path, the last few elements element-wise.
+// ----------------------------------------------------------------------------
+template <typename T, int NSRC, int NDST, int U, int USH>
+__device__ __forceinline__ void move_any(const T *const *src, T *const *dst, size_t count, int cta, int nctas) {
+    const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
+    const size_t nthr = (size_t)nctas * blockDim.x;
+    constexpr int PV = Elem<T>::PER_VEC;
+    const unsigned ms = (unsigned)((uintptr_t)src[0] & 15u), md = (unsigned)((uintptr_t)dst[0] & 15u);
+    bool uniform = true;
+#pragma unroll
+    for (int p = 1; p < NSRC; ++p) uniform = uniform && ((uintptr_t)src[p] & 15u) == ms;
+#pragma unroll
+    for (int q = 1; q < NDST; ++q) uniform = uniform && ((uintptr_t)dst[q] & 15u) == md;
+    if (!uniform) {
+        reduce_store_elem<T>(src, NSRC, dst, NDST, count, tid, nthr);
+        return;
+    }
+    const size_t head = min((size_t)(((16u - md) & 15u) / sizeof(T)), count);
+    const unsigned m = (unsigned)((ms + head * sizeof(T)) & 15u);
+    const size_t rest = count - head;
+    size_t nvec = rest / PV;
+    if (m != 0 && nvec > 0) nvec -= 1; // the shifted path reads one aligned vector more than it writes
+    const size_t tail0 = head + nvec * PV;
+    if (nvec > 0) {
+        const uint4 *vs[NSRC];
+        uint4 *vd[NDST];
+#pragma unroll
+        for (int p = 0; p < NSRC; ++p) vs[p] = (const uint4 *)((const char *)(src[p] + head) - m);
+#pragma unroll
+        for (int q = 0; q < NDST; ++q) vd[q] = (uint4 *)(dst[q] + head);
+        if (m == 0) reduce_store_vec<T, NSRC, NDST, U, NSRC == 1 && NDST == 1>(vs, vd, nvec, tid, nthr);
+        else reduce_store_vec_shifted<T, NSRC, NDST, USH>(vs, vd, nvec, m, tid, nthr);
+    }
+    // head and tail: a handful of elements, one CTA
+    if (cta == 0) {
+        if (head) reduce_store_elem<T>(src, NSRC, dst, NDST, head, threadIdx.x, blockDim.x);
+        if (tail0 < count) {
+            const T *ts[NSRC];
+            T *td[NDST];
+#pragma unroll
+            for (int p = 0; p < NSRC; ++p) ts[p] = src[p] + tail0;
+#pragma unroll
+            for (int q = 0; q < NDST; ++q) td[q] = dst[q] + tail0;
+            reduce_store_elem<T>(ts, NSRC, td, NDST, count - tail0, threadIdx.x, blockDim.x);
+        }
+    }
 }
 
 // ----------------------------------------------------------------------------
@@ -325,87 +483,44 @@ __device__ __forceinline__ bool all_aligned16(const RankView &v, size_t send_off
 // reading mine). Wire: (n-1)*S per direction.
 // ----------------------------------------------------------------------------
 template <typename T, int NR>
-__device__ __forceinline__ void allreduce_oneshot_body(const RankView &v, size_t count, int cta,
-                                                       int nctas) {
+__device__ __forceinline__ void allreduce_oneshot_body(const RankView &v, size_t count, int cta, int nctas) {
     const uint32_t e = cta_epoch(v, cta);
     cta_barrier<false>(v, e + 1, cta);
 
-    const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
-    const size_t nthr = (size_t)nctas * blockDim.x;
-    T *mine = (T *)v.recv[v.rank];
-    if (all_aligned16(v, 0, 0)) {
-        constexpr int PV = Elem<T>::PER_VEC;
-        const size_t nvec = count / PV;
-        const uint4 *src[NR];
+    const T *src[NR];
 #pragma unroll
-        for (int p = 0; p < NR; ++p) src[p] = (const uint4 *)v.send[p];
-        uint4 *dst[1] = {(uint4 *)mine};
-        reduce_store_vec<T, NR, 1, Unroll<NR>::U, NR == 1>(src, dst, nvec, tid, nthr);
-        const size_t done = nvec * PV;
-        if (done < count && cta == 0) {
-            const T *ts[MAXR];
-            for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p] + done;
-            T *td[1] = {mine + done};
-            reduce_store_elem<T>(ts, NR, td, 1, count - done, threadIdx.x, blockDim.x);
-        }
-    } else {
-        const T *ts[MAXR];
-        for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p];
-        T *td[1] = {mine};
-        reduce_store_elem<T>(ts, NR, td, 1, count, tid, nthr);
-    }
+    for (int p = 0; p < NR; ++p) src[p] = (const T *)v.send[p];
+    T *dst[1] = {(T *)v.recv[v.rank]};
+    move_any<T, NR, 1, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, count, cta, nctas);
 
     cta_barrier<false>(v, e + 2, cta); // only reads happened
     cta_finish(v, e + 2, cta);
 }
 
 // ----------------------------------------------------------------------------
-// Allreduce, two-shot fused in one pass: rank r owns slice r (16-byte aligned
-// slice boundaries), pulls that slice from every rank, sums, and pushes the result
-// into every rank's recv. Wire: 2(n-1)/n*S per direction, reads and writes overlap.
+// Allreduce, two-shot fused in one pass: rank r owns slice r (slice boundaries are whole
+// 16-byte vectors of the buffer), pulls that slice from every rank, sums, and pushes the
+// result into every rank's recv. Wire: 2(n-1)/n*S per direction, reads and writes overlap.
 // ----------------------------------------------------------------------------
 template <typename T, int NR>
-__device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t count, int cta,
-                                                       int nctas) {
+__device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t count, int cta, int nctas) {
     const uint32_t e = cta_epoch(v, cta);
     cta_barrier<false>(v, e + 1, cta);
 
-    const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
-    const size_t nthr = (size_t)nctas * blockDim.x;
     constexpr int PV = Elem<T>::PER_VEC;
-    if (all_aligned16(v, 0, 0)) {
-        const size_t nvec = count / PV;
-        const size_t per = (nvec + NR - 1) / NR;
-        const size_t v0 = min(per * (size_t)v.rank, nvec);
-        const size_t v1 = min(v0 + per, nvec);
-        const uint4 *src[NR];
-        uint4 *dst[NR];
+    // slices in units of PV elements; the last rank also takes the sub-vector remainder
+    const size_t nvec = count / PV;
+    const size_t per = (nvec + NR - 1) / NR;
+    const size_t e0 = min(per * (size_t)v.rank, nvec) * PV;
+    const size_t e1 = v.rank == NR - 1 ? count : min(per * (size_t)(v.rank + 1), nvec) * PV;
+    const T *src[NR];
+    T *dst[NR];
 #pragma unroll
-        for (int p = 0; p < NR; ++p) {
-            src[p] = (const uint4 *)v.send[p] + v0;
-            dst[p] = (uint4 *)v.recv[p] + v0;
-        }
-        reduce_store_vec<T, NR, NR, Unroll<NR>::U, NR == 1>(src, dst, v1 - v0, tid, nthr);
-        // sub-vector tail (< 16 bytes): every rank reduces it for itself
-        const size_t done = nvec * PV;
-        if (done < count && cta == 0) {
-            const T *ts[MAXR];
-            for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p] + done;
-            T *td[1] = {(T *)v.recv[v.rank] + done};
-            reduce_store_elem<T>(ts, NR, td, 1, count - done, threadIdx.x, blockDim.x);
-        }
-    } else {
-        const size_t per = (count + NR - 1) / NR;
-        const size_t e0 = min(per * (size_t)v.rank, count);
-        const size_t e1 = min(e0 + per, count);
-        const T *ts[MAXR];
-        T *td[MAXR];
-        for (int p = 0; p < NR; ++p) {
-            ts[p] = (const T *)v.send[p] + e0;
-            td[p] = (T *)v.recv[p] + e0;
-        }
-        reduce_store_elem<T>(ts, NR, td, NR, e1 - e0, tid, nthr);
+    for (int p = 0; p < NR; ++p) {
+        src[p] = (const T *)v.send[p] + e0;
+        dst[p] = (T *)v.recv[p] + e0;
     }
+    move_any<T, NR, NR, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, e1 - e0, cta, nctas);
 
     cta_barrier<true>(v, e + 2, cta); // publishes the pushed slices
     cta_finish(v, e + 2, cta);
@@ -416,38 +531,16 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
 // of every rank's recv (n-1 of them over NVLink). Wire: (n-1)*shard per direction.
 // ----------------------------------------------------------------------------
 template <typename T, int NR>
-__device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcount, int cta,
-                                               int nctas) {
+__device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcount, int cta, int nctas) {
     const uint32_t e = cta_epoch(v, cta);
     cta_barrier<false>(v, e + 1, cta);
 
-    const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
-    const size_t nthr = (size_t)nctas * blockDim.x;
-    constexpr int PV = Elem<T>::PER_VEC;
     const size_t off = sendcount * (size_t)v.rank; // elements into every recv
-    const T *s = (const T *)v.send[v.rank];
-    bool aligned = (((uintptr_t)s) & 15) == 0;
-    for (int p = 0; p < NR; ++p) aligned = aligned && ((((uintptr_t)v.recv[p]) + off * sizeof(T)) & 15) == 0;
-    if (aligned) {
-        const size_t nvec = sendcount / PV;
-        const uint4 *src[1] = {(const uint4 *)s};
-        uint4 *dst[NR];
+    const T *src[1] = {(const T *)v.send[v.rank]};
+    T *dst[NR];
 #pragma unroll
-        for (int p = 0; p < NR; ++p) dst[p] = (uint4 *)((T *)v.recv[p] + off);
-        reduce_store_vec<T, 1, NR, Unroll<NR>::U_AG, true>(src, dst, nvec, tid, nthr);
-        const size_t done = nvec * PV;
-        if (done < sendcount && cta == 0) {
-            const T *ts[1] = {s + done};
-            T *td[MAXR];
-            for (int p = 0; p < NR; ++p) td[p] = (T *)v.recv[p] + off + done;
-            reduce_store_elem<T>(ts, 1, td, NR, sendcount - done, threadIdx.x, blockDim.x);
-        }
-    } else {
-        const T *ts[1] = {s};
-        T *td[MAXR];
-        for (int p = 0; p < NR; ++p) td[p] = (T *)v.recv[p] + off;
-        reduce_store_elem<T>(ts, 1, td, NR, sendcount, tid, nthr);
-    }
+    for (int p = 0; p < NR; ++p) dst[p] = (T *)v.recv[p] + off;
+    move_any<T, 1, NR, Unroll<NR>::U_AG, Unroll<NR>::U_SH>(src, dst, sendcount, cta, nctas);
 
     cta_barrier<true>(v, e + 2, cta); // publishes the pushed shard
     cta_finish(v, e + 2, cta);
@@ -459,40 +552,106 @@ __device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcou
 // Wire: (n-1)*recvcount per direction.
 // ----------------------------------------------------------------------------
 template <typename T, int NR>
-__device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t recvcount, int cta,
-                                                    int nctas) {
+__device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t recvcount, int cta, int nctas) {
     const uint32_t e = cta_epoch(v, cta);
     cta_barrier<false>(v, e + 1, cta);
 
-    const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
-    const size_t nthr = (size_t)nctas * blockDim.x;
-    constexpr int PV = Elem<T>::PER_VEC;
     const size_t off = recvcount * (size_t)v.rank;
-    T *mine = (T *)v.recv[v.rank];
-    bool aligned = (((uintptr_t)mine) & 15) == 0;
-    for (int p = 0; p < NR; ++p) aligned = aligned && ((((uintptr_t)v.send[p]) + off * sizeof(T)) & 15) == 0;
-    if (aligned) {
-        const size_t nvec = recvcount / PV;
-        const uint4 *src[NR];
+    const T *src[NR];
 #pragma unroll
-        for (int p = 0; p < NR; ++p) src[p] = (const uint4 *)((const T *)v.send[p] + off);
-        uint4 *dst[1] = {(uint4 *)mine};
-        reduce_store_vec<T, NR, 1, Unroll<NR>::U, NR == 1>(src, dst, nvec, tid, nthr);
-        const size_t done = nvec * PV;
-        if (done < recvcount && cta == 0) {
-            const T *ts[MAXR];
-            for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p] + off + done;
-            T *td[1] = {mine + done};
-            reduce_store_elem<T>(ts, NR, td, 1, recvcount - done, threadIdx.x, blockDim.x);
-        }
-    } else {
-        const T *ts[MAXR];
-        for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p] + off;
-        T *td[1] = {mine};
-        reduce_store_elem<T>(ts, NR, td, 1, recvcount, tid, nthr);
-    }
+    for (int p = 0; p < NR; ++p) src[p] = (const T *)v.send[p] + off;
+    T *dst[1] = {(T *)v.recv[v.rank]};
+    move_any<T, NR, 1, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, recvcount, cta, nctas);
 
     cta_barrier<false>(v, e + 2, cta); // only reads happened
+    cta_finish(v, e + 2, cta);
+}
+
+// ----------------------------------------------------------------------------
+// Allreduce through NVSwitch multicast ("NVLS"): rank r owns slice r as in the two-shot
+// kernel, but ONE multimem.ld_reduce fetches the slice from all ranks and has the switch add
+// them (fp32 accumulation), and ONE multimem.st writes the result into every rank's recv.
+// Wire per GPU per direction: ~(1 + 1/n)*S instead of 2(n-1)/n*S — the only way past the
+// per-direction link rate. The summation order inside the switch is not specified: results
+// are bit-exact for integer-valued data and within 2(n-1)eps otherwise, and identical on all
+// ranks (one owner computes each slice).
+// ----------------------------------------------------------------------------
+template <typename T> struct Multimem;
+template <> struct Multimem<float> {
+    static __device__ __forceinline__ uint4 ld_reduce(const uint4 *p) {
+        uint4 r;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+        return r;
+    }
+    static __device__ __forceinline__ void st(uint4 *p, const uint4 &v) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                     "r"(v.z), "r"(v.w) : "memory");
+    }
+};
+template <> struct Multimem<__half> {
+    static __device__ __forceinline__ uint4 ld_reduce(const uint4 *p) {
+        uint4 r;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+        return r;
+    }
+    static __device__ __forceinline__ void st(uint4 *p, const uint4 &v) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f16x2 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                     "r"(v.z), "r"(v.w) : "memory");
+    }
+};
+template <> struct Multimem<__nv_bfloat16> {
+    static __device__ __forceinline__ uint4 ld_reduce(const uint4 *p) {
+        uint4 r;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+        return r;
+    }
+    static __device__ __forceinline__ void st(uint4 *p, const uint4 &v) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                     "r"(v.z), "r"(v.w) : "memory");
+    }
+};
+
+template <typename T, int NR>
+__device__ __forceinline__ void allreduce_multimem_body(const RankView &v, size_t count, int cta, int nctas) {
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
+
+    constexpr int PV = Elem<T>::PER_VEC;
+    constexpr int U = 8;
+    const size_t nvec = count / PV;
+    const size_t per = (nvec + NR - 1) / NR;
+    const size_t v0 = min(per * (size_t)v.rank, nvec);
+    const size_t n = min(v0 + per, nvec) - v0;
+    const uint4 *src = (const uint4 *)v.mc_send + v0;
+    uint4 *dst = (uint4 *)v.mc_recv + v0;
+    const size_t bdim = blockDim.x, tile = (size_t)U * bdim;
+    for (size_t t = cta; t * tile < n; t += nctas) {
+        const size_t base = t * tile + threadIdx.x;
+        uint4 val[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = base + (size_t)u * bdim;
+            if (i < n) val[u] = Multimem<T>::ld_reduce(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = base + (size_t)u * bdim;
+            if (i < n) Multimem<T>::st(dst + i, val[u]);
+        }
+    }
+    // sub-vector tail (< 16 bytes): every rank reduces it for itself over the unicast mappings
+    const size_t done = nvec * PV;
+    if (done < count && cta == 0) {
+        const T *ts[MAXR];
+        for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p] + done;
+        T *td[1] = {(T *)v.recv[v.rank] + done};
+        reduce_store_elem<T>(ts, NR, td, 1, count - done, threadIdx.x, blockDim.x);
+    }
+
+    cta_barrier<true>(v, e + 2, cta); // publishes the multicast stores
     cta_finish(v, e + 2, cta);
 }
 
@@ -500,13 +659,14 @@ __device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t re
 // __global__ wrappers. Real mode: one rank per GPU, gridDim.y == 1. Emulation
 // mode: gridDim.y virtual ranks on one GPU in one cooperative launch.
 // ----------------------------------------------------------------------------
-enum Op { OP_AR1 = 0, OP_AR2 = 1, OP_AG = 2, OP_RS = 3 };
+enum Op { OP_AR1 = 0, OP_AR2 = 1, OP_AG = 2, OP_RS = 3, OP_ARM = 4 };
 
 template <typename T, int NR, int OP>
 __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta, int nctas) {
     if (OP == OP_AR1) allreduce_oneshot_body<T, NR>(v, count, cta, nctas);
     else if (OP == OP_AR2) allreduce_twoshot_body<T, NR>(v, count, cta, nctas);
     else if (OP == OP_AG) allgather_body<T, NR>(v, count, cta, nctas);
+    else if (OP == OP_ARM) allreduce_multimem_body<T, NR>(v, count, cta, nctas);
     else reduce_scatter_body<T, NR>(v, count, cta, nctas);
 }
 

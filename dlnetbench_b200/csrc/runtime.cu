@@ -63,7 +63,15 @@ struct Drv {
     CUresult (*MemUnmap)(CUdeviceptr, size_t);
     CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t);
     CUresult (*GetErrorString)(CUresult, const char **);
-    bool ok = false;
+    // NVSwitch multicast (optional: absent or failing => the P2P kernels are used for everything)
+    CUresult (*DeviceGet)(CUdevice *, int);
+    CUresult (*DeviceGetAttribute)(int *, CUdevice_attribute, CUdevice);
+    CUresult (*MulticastCreate)(CUmemGenericAllocationHandle *, const CUmulticastObjectProp *);
+    CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice);
+    CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long);
+    CUresult (*MulticastGetGranularity)(size_t *, const CUmulticastObjectProp *, CUmulticastGranularity_flags);
+    CUresult (*MulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t);
+    bool ok = false, mc_ok = false;
 };
 static Drv drv;
 
@@ -89,6 +97,24 @@ static int load_driver() {
     DLNB_SYM(MemSetAccess, "cuMemSetAccess");
     DLNB_SYM(GetErrorString, "cuGetErrorString");
 #undef DLNB_SYM
+    {
+        struct { void **slot; const char *name; } opt[] = {
+            {(void **)&drv.DeviceGet, "cuDeviceGet"},
+            {(void **)&drv.DeviceGetAttribute, "cuDeviceGetAttribute"},
+            {(void **)&drv.MulticastCreate, "cuMulticastCreate"},
+            {(void **)&drv.MulticastAddDevice, "cuMulticastAddDevice"},
+            {(void **)&drv.MulticastBindMem, "cuMulticastBindMem"},
+            {(void **)&drv.MulticastGetGranularity, "cuMulticastGetGranularity"},
+            {(void **)&drv.MulticastUnbind, "cuMulticastUnbind"},
+        };
+        drv.mc_ok = true;
+        for (auto &o : opt) {
+            void *p = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint(o.name, &p, cudaEnableDefault, &q) != cudaSuccess || !p) drv.mc_ok = false;
+            *o.slot = p;
+        }
+    }
     drv.ok = true;
     return 0;
 }
@@ -115,6 +141,8 @@ struct Chunk {
     char *peer[MAXR] = {};                   // my mapping of world rank p's copy
     CUmemGenericAllocationHandle handle = 0; // VMM only
     std::vector<CUmemGenericAllocationHandle> imported;
+    char *mc = nullptr;                         // multicast mapping of this chunk on all ranks
+    CUmemGenericAllocationHandle mc_handle = 0;
 };
 
 struct dlnb_comm {
@@ -124,7 +152,8 @@ struct dlnb_comm {
     std::vector<cudaEvent_t> ev_done;          // completion (no timestamp: cheaper), always recorded
     std::vector<char> slot_timed;
     std::vector<char> slot_used;
-    long ctas = 0, threads = 512, algo = DLNB_ALGO_AUTO, twoshot_min_bytes = 256 * 1024, timeout_ms = 30000;
+    long ctas = 0, threads = 512, algo = DLNB_ALGO_AUTO, twoshot_min_bytes = -1 /* auto: 2 MiB / n */, timeout_ms = 30000,
+         multimem_min_bytes = 512 << 10;
 };
 
 static constexpr int MAX_COMMS = 64;
@@ -144,6 +173,11 @@ struct State {
     size_t gran = 2u << 20, min_chunk = 256u << 20, va_size = 0, va_used = 0;
     CUdeviceptr window[MAXR] = {};
     size_t bytes_in_use = 0;
+    // NVSwitch multicast view of the arena (in-switch reduction for large allreduces)
+    bool mc_enabled = false;
+    size_t mc_gran = 0, mc_va_used = 0;
+    CUdeviceptr mc_window = 0;
+    CUdevice cu_dev = 0;
     // flags / control
     char *flag_area = nullptr; // symmetric: MAX_COMMS * FLAG_BYTES_PER_COMM
     CommCtl *ctl = nullptr;    // symmetric allocation too (only used locally)
@@ -155,7 +189,7 @@ struct State {
     CommCtl *emu_ctl = nullptr;
     int emu_last_n = 0;
     // spin
-    long spin_ctas = 1, spin_threads = 32, slot_timing = 1, spin_slack_ns = 4000;
+    long spin_ctas = 1, spin_threads = 32, slot_timing = 1, spin_slack_ns = 8000;
     unsigned long long *spin_stamps = nullptr;
     unsigned spin_seq = 0;
     double spin_overhead_us = 0.0, spin_slope = 1.0;
@@ -178,6 +212,56 @@ static size_t dtype_size(int dt) { return dt == DLNB_F32 ? 4 : 2; }
 // ---------------------------------------------------------------------------
 // arena
 // ---------------------------------------------------------------------------
+// true iff `mine` is true on every rank (ranks must take the same decision about optional features)
+static bool all_ranks_agree(bool mine) {
+    std::vector<char> all((size_t)G.world);
+    char m = mine ? 1 : 0;
+    if (!G.boot.allgather(&m, 1, all.data()).empty()) return false;
+    for (char c : all)
+        if (!c) return false;
+    return true;
+}
+
+// Multicast view of a freshly mapped chunk: rank 0 creates the multicast object, everybody adds
+// its device and binds its own physical chunk at offset 0, then maps the object. Any failure on
+// any rank switches multicast off everywhere (the P2P kernels need nothing of this).
+static void chunk_add_multicast(Chunk &c) {
+    if (!G.mc_enabled) return;
+    CUmulticastObjectProp mp = {};
+    mp.numDevices = (unsigned)G.world;
+    mp.size = c.size;
+    mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    CUmemGenericAllocationHandle mc = 0;
+    int fd = -1, got = -1;
+    bool ok = true;
+    if (G.rank == 0) {
+        ok = drv.MulticastCreate(&mc, &mp) == CUDA_SUCCESS &&
+             drv.MemExportToShareableHandle(&fd, mc, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0) == CUDA_SUCCESS;
+    }
+    if (!all_ranks_agree(ok)) { if (mc) drv.MemRelease(mc); if (fd >= 0) ::close(fd); G.mc_enabled = false; return; }
+    if (!G.boot.bcast_fd(fd, got).empty()) ok = false;
+    if (fd >= 0) ::close(fd);
+    if (ok && G.rank != 0)
+        ok = drv.MemImportFromShareableHandle(&mc, (void *)(uintptr_t)got, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR) == CUDA_SUCCESS;
+    if (got >= 0) ::close(got);
+    if (ok) ok = drv.MulticastAddDevice(mc, G.cu_dev) == CUDA_SUCCESS;
+    if (!all_ranks_agree(ok)) { if (mc) drv.MemRelease(mc); G.mc_enabled = false; return; } // all devices added before any bind
+    ok = drv.MulticastBindMem(mc, 0, c.handle, 0, c.size, 0) == CUDA_SUCCESS;
+    CUdeviceptr va = G.mc_window + G.mc_va_used;
+    if (ok) ok = drv.MemMap(va, c.size, 0, mc, 0) == CUDA_SUCCESS;
+    if (ok) {
+        CUmemAccessDesc acc = {};
+        acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        acc.location.id = G.device;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        ok = drv.MemSetAccess(va, c.size, &acc, 1) == CUDA_SUCCESS;
+    }
+    if (!all_ranks_agree(ok)) { G.mc_enabled = false; return; } // leaks this one object; the process goes on with P2P
+    c.mc = (char *)va;
+    c.mc_handle = mc;
+    G.mc_va_used += c.size;
+}
+
 static int arena_grow(size_t need) {
     Chunk c;
     const size_t want = std::max(need, G.min_chunk);
@@ -232,6 +316,7 @@ static int arena_grow(size_t need) {
         }
         c.local = c.peer[G.rank];
         G.va_used += c.size;
+        chunk_add_multicast(c);
     } else { // ARENA_IPC (diagnostic fallback: cudaMalloc + cudaIpc handles)
         c.size = round_up(want, 2u << 20);
         void *p = nullptr;
@@ -283,6 +368,14 @@ static char *translate(const void *p, int wr) {
     return nullptr;
 }
 
+// multicast address of the symmetric allocation holding `p` (null if it has none)
+static char *translate_mc(const void *p) {
+    const char *q = (const char *)p;
+    for (const Chunk &c : G.chunks)
+        if (q >= c.local && q < c.local + c.size) return c.mc ? c.mc + (q - c.local) : nullptr;
+    return nullptr;
+}
+
 // ---------------------------------------------------------------------------
 // init / finalize
 // ---------------------------------------------------------------------------
@@ -326,6 +419,7 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
         G.kind = ARENA_LOCAL;
     }
     if (const char *m = getenv("DLNB_CHUNK_MB")) G.min_chunk = (size_t)atol(m) << 20;
+    if (const char *m = getenv("DLNB_SPIN_SLACK_NS")) G.spin_slack_ns = std::max(0L, atol(m));
 
     if (G.kind == ARENA_VMM) {
         if (load_driver()) return 1;
@@ -339,6 +433,31 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
         if (const char *v = getenv("DLNB_ARENA_VA_GB")) gb = (size_t)atol(v);
         G.va_size = gb << 30;
         for (int r = 0; r < world; ++r) DRV_TRY(drv.MemAddressReserve(&G.window[r], G.va_size, G.gran, 0, 0));
+        // optional: NVSwitch multicast view of the arena
+        const char *mcenv = getenv("DLNB_MULTICAST");
+        bool want = drv.mc_ok && !(mcenv && !strcmp(mcenv, "0"));
+        if (want) {
+            int sup = 0;
+            want = drv.DeviceGet(&G.cu_dev, device) == CUDA_SUCCESS &&
+                   drv.DeviceGetAttribute(&sup, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, G.cu_dev) == CUDA_SUCCESS && sup;
+        }
+        if (want) {
+            CUmulticastObjectProp mp = {};
+            mp.numDevices = (unsigned)world;
+            mp.size = G.min_chunk;
+            mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+            size_t g = 0;
+            want = drv.MulticastGetGranularity(&g, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED) == CUDA_SUCCESS && g > 0 && g <= (1u << 30);
+            if (want) G.mc_gran = g;
+        }
+        if (want) want = drv.MemAddressReserve(&G.mc_window, G.va_size, std::max(G.gran, G.mc_gran), 0, 0) == CUDA_SUCCESS;
+        G.mc_enabled = all_ranks_agree(want);
+        if (G.mc_enabled) {
+            G.gran = std::max(G.gran, G.mc_gran); // chunk sizes must suit both the allocation and the multicast object
+            G.min_chunk = std::max(G.min_chunk, G.gran);
+        }
+        if (getenv("DLNB_DEBUG") && rank == 0)
+            fprintf(stderr, "[dlnb] multicast %s (granularity %zu MiB)\n", G.mc_enabled ? "on" : "off", G.mc_gran >> 20);
     }
 
     int lo = 0, hi = 0;
@@ -383,6 +502,11 @@ extern "C" int dlnb_finalize(void) {
     G.comms.clear();
     for (Chunk &c : G.chunks) {
         if (G.kind == ARENA_VMM) {
+            if (c.mc) {
+                drv.MemUnmap((CUdeviceptr)c.mc, c.size);
+                drv.MulticastUnbind(c.mc_handle, G.cu_dev, 0, c.size);
+                drv.MemRelease(c.mc_handle);
+            }
             for (int r = 0; r < G.world; ++r)
                 if (c.peer[r]) drv.MemUnmap((CUdeviceptr)c.peer[r], c.size);
             for (auto h : c.imported)
@@ -401,6 +525,7 @@ extern "C" int dlnb_finalize(void) {
     if (G.kind == ARENA_VMM)
         for (int r = 0; r < G.world; ++r)
             if (G.window[r]) drv.MemAddressFree(G.window[r], G.va_size);
+    if (G.kind == ARENA_VMM && G.mc_window) drv.MemAddressFree(G.mc_window, G.va_size);
     if (G.emu_flags) cudaFree(G.emu_flags);
     if (G.emu_ctl) cudaFree(G.emu_ctl);
     if (G.flush_buf) cudaFree(G.flush_buf);
@@ -453,6 +578,7 @@ extern "C" long dlnb_get(const char *key) {
     if (!strcmp(key, "slot_timing")) return G.slot_timing;
     if (!strcmp(key, "spin_slack_ns")) return G.spin_slack_ns;
     if (!strcmp(key, "sms")) return G.sms;
+    if (!strcmp(key, "multicast")) return G.mc_enabled ? 1 : 0;
     return -1;
 }
 
@@ -498,6 +624,7 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
     if (const char *v = getenv("DLNB_THREADS")) c->threads = atol(v);
     if (const char *v = getenv("DLNB_ALGO")) c->algo = atol(v);
     if (const char *v = getenv("DLNB_TWOSHOT_MIN_BYTES")) c->twoshot_min_bytes = atol(v);
+    if (const char *v = getenv("DLNB_MULTIMEM_MIN_BYTES")) c->multimem_min_bytes = atol(v);
     G.comms.push_back(c);
     *out = c;
     return 0;
@@ -520,6 +647,7 @@ extern "C" int dlnb_comm_set(dlnb_comm_t c, const char *key, long value) {
     else if (!strcmp(key, "threads")) c->threads = value;
     else if (!strcmp(key, "algo")) c->algo = value;
     else if (!strcmp(key, "twoshot_min_bytes")) c->twoshot_min_bytes = value;
+    else if (!strcmp(key, "multimem_min_bytes")) c->multimem_min_bytes = value;
     else if (!strcmp(key, "timeout_ms")) c->timeout_ms = value;
     else return fail("dlnb_comm_set: unknown key %s", key);
     return 0;
@@ -530,6 +658,7 @@ extern "C" long dlnb_comm_get(dlnb_comm_t c, const char *key) {
     if (!strcmp(key, "threads")) return c->threads;
     if (!strcmp(key, "algo")) return c->algo;
     if (!strcmp(key, "twoshot_min_bytes")) return c->twoshot_min_bytes;
+    if (!strcmp(key, "multimem_min_bytes")) return c->multimem_min_bytes;
     if (!strcmp(key, "timeout_ms")) return c->timeout_ms;
     if (!strcmp(key, "id")) return c->id;
     return -1;
@@ -617,6 +746,7 @@ static size_t work_bytes(int op, int n, size_t count, size_t esz) {
     switch (op) {
     case OP_AR1: return count * esz;
     case OP_AR2: return count * esz / (size_t)n;
+    case OP_ARM: return count * esz / (size_t)n;
     case OP_AG: return count * esz;
     default: return count * esz;
     }
@@ -633,8 +763,10 @@ static int pick_grid(long want, int dtype, int op, int n, int threads, size_t by
         g = want;
     } else if (n == 1) {
         g = (long)G.sms * 4;
+    } else if (op == OP_ARM) {
+        g = 16; // the switch does the adding: 16 CTAs saturate the links (measured: more is slower)
     } else {
-        g = 64; // NVLink-bound: enough bytes in flight without taking every SM
+        g = 128; // NVLink-bound peer loads/stores: measured best for >= 64 MB, harmless below
     }
     // no more CTAs than 16-byte vectors / threads
     const size_t vecs = bytes / 16 + 1;
@@ -667,11 +799,27 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
     else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range (communicator has %d)", slot, c->num_slots);
     if (count && (!send || !recv)) return fail("null buffer");
     const size_t esz = dtype_size(c->dtype);
+    char *mc_s = nullptr, *mc_r = nullptr;
     if (op == OP_AR1 || op == OP_AR2) {
         const size_t bytes = count * esz;
-        const bool small = (size_t)c->twoshot_min_bytes > bytes;
+        // measured cross-over (B200): one-shot wins up to ~1 MiB on 2 GPUs, ~256 KiB on 8
+        const size_t two_min = c->twoshot_min_bytes >= 0 ? (size_t)c->twoshot_min_bytes : (size_t)(2 << 20) / (size_t)c->n;
+        const bool small = two_min > bytes;
+        // in-switch reduction needs the multicast view of both buffers, the whole world in the
+        // group (the multicast object spans every rank) and 16-byte aligned buffers
+        if (c->n > 1 && c->n == G.world && G.mc_enabled && (c->algo == DLNB_ALGO_MULTIMEM || c->algo == DLNB_ALGO_AUTO) &&
+            (((uintptr_t)send | (uintptr_t)recv) & 15) == 0) {
+            mc_s = translate_mc(send);
+            mc_r = translate_mc(recv);
+        }
+        const bool mc_ok = mc_s && mc_r;
+        if (c->algo == DLNB_ALGO_MULTIMEM && !mc_ok)
+            return fail("multimem allreduce requested but unavailable (multicast %s, group %d of world %d)",
+                        G.mc_enabled ? "on" : "off", c->n, G.world);
         if (c->algo == DLNB_ALGO_ONESHOT) op = OP_AR1;
         else if (c->algo == DLNB_ALGO_TWOSHOT) op = OP_AR2;
+        else if (c->algo == DLNB_ALGO_MULTIMEM) op = OP_ARM;
+        else if (mc_ok && c->n >= 4 && bytes >= (size_t)c->multimem_min_bytes) op = OP_ARM; // n < 4: P2P moves fewer bytes
         else op = (c->n == 1 || small) ? OP_AR1 : OP_AR2;
     }
     if (join_streams()) return 1;
@@ -690,6 +838,8 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
             v.recv[i] = r;
             v.flags[i] = (uint32_t *)translate(G.flag_area + (size_t)c->id * FLAG_BYTES_PER_COMM, c->ranks[i]);
         }
+        v.mc_send = op == OP_ARM ? mc_s : nullptr;
+        v.mc_recv = op == OP_ARM ? mc_r : nullptr;
         v.ctl = G.ctl + c->id;
         v.host_error = G.host_error_dev;
         v.timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;

