@@ -162,12 +162,12 @@ struct Section {
 };
 
 // ---- CLI: positional required arguments, then -w/-r/-d/-m/-h (dp.cpp:108-122, fsdp.cpp:165-180);
-//      additive: -t <fp32|fp16|bf16>, -a <auto|oneshot|twoshot>, -c <ctas>, -s <spin ctas> ------------
+//      additive: -t <fp32|fp16|bf16>, -a <auto|oneshot|twoshot|multimem>, -c <ctas>, -s <spin ctas>, -g ---
 struct Cli {
     std::vector<std::string> positional;
     int warmup = 3, runs = 5, min_exectime = 0, ctas = 0, spin_ctas = 1;
     std::string devices, dtype = "fp16", algo = "auto";
-    bool help = false, ok = true;
+    bool help = false, ok = true, graph = false;
 };
 inline Cli parse_cli(int argc, char **argv) {
     Cli c;
@@ -176,6 +176,7 @@ inline Cli parse_cli(int argc, char **argv) {
         auto value = [&](std::string &dst) { if (i + 1 < argc) dst = argv[++i]; else c.ok = false; };
         auto ivalue = [&](int &dst) { std::string s; value(s); if (c.ok) dst = atoi(s.c_str()); };
         if (a == "-h") c.help = true;
+        else if (a == "-g") c.graph = true;
         else if (a == "-w") ivalue(c.warmup);
         else if (a == "-r") ivalue(c.runs);
         else if (a == "-m") ivalue(c.min_exectime);
@@ -196,9 +197,10 @@ inline void print_options_help() {
            "  -d <devices>       Comma-separated list of devices (default: \"\")\n"
            "  -m <min_exectime>  Minimum total execution time in seconds (overrides runs) (default: 0)\n"
            "  -t <dtype>         fp32 | fp16 | bf16 (default: fp16)          [b200 addition]\n"
-           "  -a <algo>          auto | oneshot | twoshot allreduce (default: auto)  [b200 addition]\n"
+           "  -a <algo>          auto | oneshot | twoshot | multimem allreduce (default: auto)  [b200 addition]\n"
            "  -c <ctas>          CTAs per collective kernel, 0 = auto        [b200 addition]\n"
            "  -s <spin_ctas>     CTAs of the compute-emulation kernel (default: 1)  [b200 addition]\n"
+           "  -g                 Capture one iteration as a CUDA graph and replay it  [b200 addition]\n"
            "  -h                 Show help\n");
 }
 inline int dtype_from_name(const std::string &s) {
@@ -211,6 +213,7 @@ inline int algo_from_name(const std::string &s) {
     if (s == "auto") return DLNB_ALGO_AUTO;
     if (s == "oneshot") return DLNB_ALGO_ONESHOT;
     if (s == "twoshot") return DLNB_ALGO_TWOSHOT;
+    if (s == "multimem") return DLNB_ALGO_MULTIMEM;
     return -1;
 }
 inline size_t dtype_bytes(int dt) { return dt == DLNB_F32 ? 4 : 2; }
@@ -230,6 +233,25 @@ inline long loop_iters_from_env() {
     const char *v = getenv("DLNB_LOOP_ITERS");
     return v ? atol(v) : -1; // -1: forever
 }
+
+// One proxy iteration, either issued call by call or captured once and replayed (-g).
+template <typename Fn> struct IterationRunner {
+    Fn body;
+    dlnb_graph_t graph = nullptr;
+    bool use_graph;
+    IterationRunner(Fn f, bool g) : body(f), use_graph(g) {}
+    void operator()() {
+        if (!use_graph) { body(); return; }
+        if (!graph) {
+            check(dlnb_graph_begin(), "graph begin");
+            body();
+            check(dlnb_graph_end(&graph), "graph end");
+        }
+        check(dlnb_graph_launch(graph), "graph launch");
+        check(dlnb_compute_sync(), "graph sync");
+    }
+};
+template <typename Fn> inline IterationRunner<Fn> make_runner(Fn f, bool g) { return IterationRunner<Fn>(f, g); }
 
 inline float median(std::vector<float> v) {
     if (v.empty()) return 0.f;

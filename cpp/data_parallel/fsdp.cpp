@@ -174,11 +174,12 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
     b200::check(dlnb_spin_calibrate(&spin_overhead_us, &spin_slope), "spin calibration");
     b200::host_barrier();
 
-    auto iteration = [&]() {
+    auto plain_iteration = [&]() {
         run_fsdp<T>(shard_params.data(), allgather_buf, allreduce_params.data(), fwd_rt_whole_unit, bwd_rt_whole_unit,
                     num_units, sharding_factor, max_params_per_shard.data(), num_replicas, unit_comm_proxy,
                     allreduce_comm_proxy);
     };
+    auto iteration = b200::make_runner(plain_iteration, cli.graph);
     std::vector<float> warmup_times;
     for (int i = 0; i < cli.warmup; i++) {
         const double t0 = b200::wtime();
@@ -230,10 +231,11 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
     const uint64_t reducescatter_msg_size = max_params_per_shard[0] * sizeof(T);
     const uint64_t lower_bound_us = (uint64_t)(num_units - 1) * (uint64_t)fwd_rt_whole_unit + (uint64_t)num_units * (uint64_t)bwd_rt_whole_unit;
     const std::vector<float> device_ms_max = b200::max_over_ranks(device_ms);
-    // device time of the most recent blocking collective = the last ReduceScatter (unit 0)
-    const float last_rs_ms = unit_comm_proxy->slot_ms(-1);
+    // device time of the most recent blocking collective = the last ReduceScatter (unit 0);
+    // slots are not host-visible inside a graph replay
+    const float last_rs_ms = cli.graph ? 0.f : unit_comm_proxy->slot_ms(-1);
     const int F = (int)sharding_factor;
-    const double rs_bus = F > 1 ? (double)(F - 1) / F * (double)allgather_msg_size / (last_rs_ms * 1e-3) / 1e9
+    const double rs_bus = last_rs_ms <= 0 ? 0.0 : F > 1 ? (double)(F - 1) / F * (double)allgather_msg_size / (last_rs_ms * 1e-3) / 1e9
                                 : 2.0 * (double)reducescatter_msg_size / (last_rs_ms * 1e-3) / 1e9;
 
     b200::Section fsdp("fsdp", "FSDP metrics");
@@ -271,6 +273,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         .put("spin_overhead_us", spin_overhead_us)
         .put("spin_slope", spin_slope)
         .put("spin_ctas", cli.spin_ctas)
+        .put("cuda_graph", cli.graph)
         .put("kernel_launches", (uint64_t)dlnb_launch_count());
     fsdp.emit();
 

@@ -88,6 +88,11 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_iter_begin": (i, []),
         "dlnb_iter_end": (i, [C.POINTER(C.c_float)]),
         "dlnb_batch_begin": (i, []),
+        "dlnb_graph_begin": (i, []),
+        "dlnb_graph_end": (i, [pvp]),
+        "dlnb_graph_launch": (i, [vp]),
+        "dlnb_graph_kernel_nodes": (i, [vp]),
+        "dlnb_graph_destroy": (i, [vp]),
         "dlnb_slot_elapsed": (i, [vp, i, C.POINTER(C.c_float)]),
         "dlnb_memcpy_h2d": (i, [vp, vp, sz]),
         "dlnb_memcpy_d2h": (i, [vp, vp, sz]),
@@ -244,6 +249,35 @@ def spin_calibrate() -> tuple[float, float]:
 
 def iter_begin() -> None:
     check(lib().dlnb_iter_begin())
+
+
+class Graph:
+    """One captured proxy iteration: `with capi.Graph() as g: ...issue spins and collectives...`, then g.launch()."""
+
+    def __init__(self):
+        self.h = C.c_void_p()
+
+    def __enter__(self):
+        check(lib().dlnb_graph_begin())
+        return self
+
+    def __exit__(self, et, ev, tb):
+        check(lib().dlnb_graph_end(C.byref(self.h)))
+        return False
+
+    def launch(self):
+        check(lib().dlnb_graph_launch(self.h))
+
+    def kernel_nodes(self) -> int:
+        return lib().dlnb_graph_kernel_nodes(self.h)
+
+    def destroy(self):
+        check(lib().dlnb_graph_destroy(self.h))
+        self.h = C.c_void_p()
+
+
+def compute_sync() -> None:
+    check(lib().dlnb_compute_sync())
 
 
 def batch_begin() -> None:

@@ -168,6 +168,7 @@ struct State {
     cudaEvent_t ev_join = nullptr, ev_copy = nullptr, ev_iter0 = nullptr, ev_iter1 = nullptr, ev_tmp0 = nullptr,
                 ev_tmp1 = nullptr;
     bool compute_dirty = false, copy_dirty = false;
+    bool capturing = false, comm_in_capture = false; // between dlnb_graph_begin and dlnb_graph_end
     // arena
     std::vector<Chunk> chunks;
     size_t gran = 2u << 20, min_chunk = 256u << 20, va_size = 0, va_used = 0;
@@ -684,6 +685,7 @@ extern "C" int dlnb_compute_spin(double usec) {
 }
 extern "C" int dlnb_compute_sync(void) {
     NEED_INIT();
+    if (G.capturing) return 0;
     CU_TRY(cudaStreamSynchronize(G.s_compute));
     return 0;
 }
@@ -779,6 +781,10 @@ static int pick_grid(long want, int dtype, int op, int n, int threads, size_t by
 
 static int join_streams() {
     // the collective may not start before compute / copies enqueued so far
+    if (G.capturing && !G.comm_in_capture) { // fork the communication stream into the capture
+        G.compute_dirty = true;
+        G.comm_in_capture = true;
+    }
     if (G.compute_dirty) {
         CU_TRY(cudaEventRecord(G.ev_join, G.s_compute));
         CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_join, 0));
@@ -823,7 +829,8 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
         else op = (c->n == 1 || small) ? OP_AR1 : OP_AR2;
     }
     if (join_streams()) return 1;
-    if (G.slot_timing) CU_TRY(cudaEventRecord(c->ev_start[slot], G.s_comm));
+    const bool timed = G.slot_timing && !G.capturing;
+    if (timed) CU_TRY(cudaEventRecord(c->ev_start[slot], G.s_comm));
     if (count) {
         EmuViews ev;
         RankView &v = ev.v[0];
@@ -850,9 +857,14 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
         if (e != cudaSuccess) return fail("collective launch failed: %s", cudaGetErrorString(e));
         G.launches++;
     }
-    if (G.slot_timing) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+    if (G.capturing) { // completion is the graph's: nothing for the host to wait on per slot
+        c->slot_used[slot] = 0;
+        c->slot_timed[slot] = 0;
+        return 0;
+    }
+    if (timed) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
     CU_TRY(cudaEventRecord(c->ev_done[slot], G.s_comm));
-    c->slot_timed[slot] = G.slot_timing ? 1 : 0;
+    c->slot_timed[slot] = timed ? 1 : 0;
     c->slot_used[slot] = 1;
     return 0;
 }
@@ -876,6 +888,7 @@ extern "C" int dlnb_ireduce_scatter(dlnb_comm_t c, const void *send, void *recv,
 }
 extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
     NEED_INIT();
+    if (G.capturing) return 0; // ordering inside a captured iteration is the streams'; the host waits on the replay
     if (!c) return fail("null communicator");
     if (slot == -1) slot = c->num_slots;
     else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
@@ -885,6 +898,7 @@ extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
 }
 extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
     NEED_INIT();
+    if (G.capturing) return 0;
     if (!c) return fail("null communicator");
     if (nslots > c->num_slots) nslots = c->num_slots;
     // the communication stream is ordered: waiting for the newest used slot suffices,
@@ -895,6 +909,7 @@ extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
 }
 extern "C" int dlnb_barrier(dlnb_comm_t c) {
     NEED_INIT();
+    if (G.capturing) return 0;
     if (!c) return fail("null communicator");
     CU_TRY(cudaStreamSynchronize(G.s_comm));
     return check_watchdog();
@@ -955,6 +970,82 @@ extern "C" int dlnb_iter_end(float *ms) {
     CU_TRY(cudaEventSynchronize(G.ev_iter1));
     if (ms) CU_TRY(cudaEventElapsedTime(ms, G.ev_iter0, G.ev_iter1));
     return check_watchdog();
+}
+
+// ---------------------------------------------------------------------------
+// whole-iteration CUDA graphs (launch-bound configurations: thousands of small buckets)
+// ---------------------------------------------------------------------------
+struct dlnb_graph {
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+};
+
+extern "C" int dlnb_graph_begin(void) {
+    NEED_INIT();
+    if (G.capturing) return fail("dlnb_graph_begin: a capture is already open");
+    CU_TRY(cudaStreamSynchronize(G.s_compute));
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    CU_TRY(cudaStreamSynchronize(G.s_copy));
+    G.compute_dirty = G.copy_dirty = false;
+    CU_TRY(cudaStreamBeginCapture(G.s_compute, cudaStreamCaptureModeRelaxed));
+    G.capturing = true;
+    G.comm_in_capture = false;
+    return 0;
+}
+extern "C" int dlnb_graph_end(dlnb_graph_t *out) {
+    NEED_INIT();
+    if (!G.capturing) return fail("dlnb_graph_end without dlnb_graph_begin");
+    if (!out) return fail("dlnb_graph_end: null out pointer");
+    cudaError_t e = cudaSuccess;
+    if (G.comm_in_capture) { // join the communication stream back into the origin stream
+        e = cudaEventRecord(G.ev_join, G.s_comm);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(G.s_compute, G.ev_join, 0);
+    }
+    dlnb_graph *g = new dlnb_graph;
+    cudaError_t e2 = cudaStreamEndCapture(G.s_compute, &g->graph);
+    G.capturing = G.comm_in_capture = false;
+    G.compute_dirty = G.copy_dirty = false;
+    if (e != cudaSuccess || e2 != cudaSuccess || !g->graph) {
+        delete g;
+        return fail("graph capture failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+    }
+    e = cudaGraphInstantiate(&g->exec, g->graph, 0);
+    if (e != cudaSuccess) {
+        cudaGraphDestroy(g->graph);
+        delete g;
+        return fail("cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+    }
+    *out = g;
+    return 0;
+}
+extern "C" int dlnb_graph_launch(dlnb_graph_t g) {
+    NEED_INIT();
+    if (!g || !g->exec) return fail("dlnb_graph_launch: null graph");
+    if (G.capturing) return fail("dlnb_graph_launch inside a capture");
+    CU_TRY(cudaGraphLaunch(g->exec, G.s_compute));
+    G.launches++; // one launch call; the kernels inside are counted by dlnb_graph_kernel_nodes()
+    G.compute_dirty = true;
+    return 0;
+}
+extern "C" int dlnb_graph_kernel_nodes(dlnb_graph_t g) {
+    if (!g || !g->graph) return -1;
+    size_t n = 0;
+    if (cudaGraphGetNodes(g->graph, nullptr, &n) != cudaSuccess) return -1;
+    std::vector<cudaGraphNode_t> nodes(n);
+    if (n && cudaGraphGetNodes(g->graph, nodes.data(), &n) != cudaSuccess) return -1;
+    int k = 0;
+    for (auto nd : nodes) {
+        cudaGraphNodeType t;
+        if (cudaGraphNodeGetType(nd, &t) == cudaSuccess && t == cudaGraphNodeTypeKernel) ++k;
+    }
+    return k;
+}
+extern "C" int dlnb_graph_destroy(dlnb_graph_t g) {
+    if (!g) return 0;
+    if (g->exec) cudaGraphExecDestroy(g->exec);
+    if (g->graph) cudaGraphDestroy(g->graph);
+    delete g;
+    return 0;
 }
 
 // ---------------------------------------------------------------------------

@@ -35,6 +35,7 @@ extern "C" {
 #define DLNB_MAX_RANKS 8
 
 typedef struct dlnb_comm *dlnb_comm_t;
+typedef struct dlnb_graph *dlnb_graph_t;
 
 /* element types; reference: cpp/data_types.hpp:36-51 (_FLOAT / NCCL_FLOAT_TYPE) */
 enum dlnb_dtype { DLNB_F32 = 0, DLNB_F16 = 1, DLNB_BF16 = 2 };
@@ -151,6 +152,21 @@ int dlnb_batch_begin(void);
 /* device time of the most recent collective recorded in `slot` (ms); slot -1 = the most
  * recent BLOCKING call (those use an internal slot, never one of the caller's) */
 int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms);
+
+/* ---- whole-iteration CUDA graphs ---------------------------------------------------
+ * Added (no reference counterpart). For launch-bound configurations (vit_h with 4000 buckets:
+ * 9 us of compute per bucket against ~30 us of host launch work) one proxy iteration —
+ * every dlnb_compute_spin and collective issued between begin and end — is captured once and
+ * replayed with a single launch. Inside a capture dlnb_wait / dlnb_waitall / dlnb_barrier /
+ * dlnb_compute_sync return at once (the streams keep the order); after dlnb_graph_launch the
+ * host waits with dlnb_compute_sync() or dlnb_iter_end(). The kernels keep their barrier
+ * generations and spin stamps in device memory, so a replay needs no patched arguments.
+ * All ranks must capture the same sequence and launch the same number of replays. */
+int dlnb_graph_begin(void);
+int dlnb_graph_end(dlnb_graph_t *out);
+int dlnb_graph_launch(dlnb_graph_t g);
+int dlnb_graph_kernel_nodes(dlnb_graph_t g); /* kernels inside the graph (for launch accounting) */
+int dlnb_graph_destroy(dlnb_graph_t g);
 
 /* ---- buffer helpers (tests, bench, end-to-end path) ----------------------------- */
 int dlnb_memcpy_h2d(void *dst, const void *src, size_t bytes);

@@ -144,6 +144,24 @@ def main():
     for t in recv:
         expect(capi.verify_sum_pattern(t.data, count, 0, capi.F16, 1, 0, list(range(world))) == 0, "dp iteration result")
     expect(6.0 <= ms < 8.0, f"dp iteration took {ms:.3f} ms for 6 ms of emulated compute")
+
+    # ---- the same iteration captured as a CUDA graph and replayed: generations live in device memory
+    for t in recv:
+        t.fill(0)
+    with capi.Graph() as g:
+        capi.compute_spin(1000.0)
+        for i in range(8):
+            capi.compute_spin(250.0)
+            comm.Iallreduce(send[i].data, recv[i].data, count, i)
+        comm.WaitAll(8)
+    for rep in range(3):
+        capi.iter_begin()
+        g.launch()
+        gms = capi.iter_end()
+        expect(3.0 <= gms < 4.0, f"graph replay {rep} took {gms:.3f} ms for 3 ms of emulated compute")
+    for t in recv:
+        expect(capi.verify_sum_pattern(t.data, count, 0, capi.F16, 1, 0, list(range(world))) == 0, "graph replay result")
+    g.destroy()
     comm.finalize()
 
     arena = capi.lib().dlnb_arena_kind().decode()

@@ -194,3 +194,32 @@ def test_collective_waits_for_compute(dl):
     ms = dl.iter_end()
     assert ms >= 29.0, ms
     comm.finalize()
+
+
+def test_cuda_graph_replay_of_a_dp_iteration(dl, oracle):
+    """A captured iteration (spin -> allreduce chains) replays with one launch, gives the same
+    bits every time and lasts the sum of the emulated compute."""
+    dtype, count, buckets = dl.F16, 200_003, 40
+    comm = dl.B200Communicator([0], num_slots=buckets, dtype=dtype)
+    send = [dl.Tensor(count, dtype) for _ in range(buckets)]
+    recv = [dl.Tensor(count, dtype) for _ in range(buckets)]
+    for i, t in enumerate(send):
+        t.fill(dl.PAT_UNIFORM, 100 + i, 0)
+    with dl.Graph() as g:
+        dl.compute_spin(500.0)
+        for i in range(buckets):
+            dl.compute_spin(50.0)
+            comm.Iallreduce(send[i].data, recv[i].data, count, i)
+        comm.WaitAll(buckets)  # a no-op inside the capture
+    assert g.kernel_nodes() == 1 + 2 * buckets
+    for rep in range(3):
+        for t in recv:
+            t.fill(dl.PAT_ZERO)
+        dl.iter_begin()
+        g.launch()
+        ms = dl.iter_end()
+        assert 2.5 <= ms <= 2.5 + 0.15, ms
+        for i in (0, buckets - 1):
+            assert dl.verify_sum_pattern(recv[i].data, count, 0, dtype, dl.PAT_UNIFORM, 100 + i, [0]) == 0
+    g.destroy()
+    comm.finalize()
