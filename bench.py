@@ -115,6 +115,35 @@ def run_reference_dp(model, buckets, ranks, warmup, steps, scale):
                       f"divided by {scale}, {buckets} buckets, {ranks} rank(s); value = median iteration x {scale}"}
 
 
+class Plumbing:
+    """Cross-rank plumbing of the bench (torch.distributed when there is more than one rank):
+    barrier + device synchronize on both sides of the timed region, and max over ranks."""
+
+    def __init__(self, dist, device):
+        self.dist, self.device = dist, device
+
+    def _sync(self):
+        if self.device == "cuda":
+            import torch
+
+            torch.cuda.synchronize()
+
+    def barrier(self):
+        self._sync()
+        if self.dist is not None:
+            self.dist.barrier()
+        self._sync()
+
+    def max_over_ranks(self, x):
+        if self.dist is None:
+            return x
+        import torch
+
+        t = torch.tensor([x], dtype=torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+
 def pick_scale(model_size, ranks, budget_bytes=16e9):
     scale = 1
     while ranks * 2 * 4 * model_size / scale > budget_bytes:
@@ -195,18 +224,8 @@ def main():
         g.fill(capi.PAT_INT, 0, rank)  # integer-valued gradients: exact sums, checked below
     spin_overhead_us, spin_slope = capi.spin_calibrate()
 
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    plumb = Plumbing(dist, "cuda")
+    barrier, max_over_ranks = plumb.barrier, plumb.max_over_ranks
 
     def step(e2e=False, host=None, probe=None):
         """run_data_parallel (dp.cpp:87-106) over the C ABI."""

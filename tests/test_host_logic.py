@@ -153,3 +153,37 @@ def test_bucket_split_in_bench_matches_oracle(oracle):
 
     for m, n in ((8_030_261_248, 240), (632_404_480, 1000), (774_030_080, 10), (17, 5)):
         assert bench.bucket_sizes(m, n) == oracle.bucket_sizes(m, n)
+
+
+def _gloo_rank(rank, world, port, q):
+    import torch.distributed as dist
+
+    import bench
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    p = bench.Plumbing(dist, "cpu")
+    p.barrier()
+    q.put((rank, p.max_over_ranks(10.0 + rank), p.max_over_ranks(5.0 - rank)))
+    dist.destroy_process_group()
+
+
+def test_bench_plumbing_world_size_2_gloo():
+    """The N>1 plumbing of bench.py (barrier, max over ranks) on CPU with gloo, world_size 2."""
+    import socket
+
+    import torch.multiprocessing as mp
+
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_rank, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert got == [(0, 11.0, 5.0), (1, 11.0, 5.0)]
