@@ -269,11 +269,13 @@ def main():
     # nothing cached), ONE CUDA-event pair around the batch -> average launch duration. The
     # per-slot events inside a step (kern_in_step_ms) also contain the stream-wait-to-launch gap.
     barrier()
+    capi.set_option("slot_timing", 0)  # no per-launch timing events between the kernels of the batch
     capi.iter_begin()
     for i in range(a.buckets):
         comm.Iallreduce(grad[i].data, summed[i].data, sizes[i], i)
     comm.WaitAll(a.buckets)
     kern_avg_ms = max_over_ranks(capi.iter_end() / a.buckets)
+    capi.set_option("slot_timing", 1)
 
     # ---- end to end: host buffers in, host result out, copies inside the timed region
     e2e = None
