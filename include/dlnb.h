@@ -112,7 +112,11 @@ int dlnb_compute_sync(void);
  * isolated spin (reported, not subtracted). */
 int dlnb_spin_calibrate(double *overhead_us, double *slope);
 /* "spin_ctas" / "spin_threads": footprint of the spin kernel (SM share of the emulated
- * compute); "spin_slack_ns": chaining window; "slot_timing": record a start event per slot. */
+ * compute); "spin_slack_ns": chaining window; "slot_timing": record a start event per slot;
+ * "lanes" (1 or 2, default 2; all ranks alike): with 2, consecutive small allreduces (grid
+ * <= 64 CTAs) alternate between two ordered communication streams with their own flag rows so
+ * that their barrier latencies overlap; allgather, reduce-scatter and large allreduces are
+ * ordered after and before everything else, as with one stream. */
 int dlnb_set(const char *key, long value);
 long dlnb_get(const char *key);
 
