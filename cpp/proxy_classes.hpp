@@ -87,13 +87,17 @@ class B200Communicator : public ProxyCommunicator {
     }
     std::string get_name() override { return "B200P2P"; }
 
-    // Pipeline / expert-parallel traffic: used only by the hybrid proxies, which are outside
-    // this build (the data-parallel drivers never call them — no call site in dp.cpp/fsdp.cpp).
+    // Stage-to-stage traffic of the pipeline proxies: a rendezvous put over peer memory.
+    void send(const void *buf, int count, int dest) override { B200_CHECK(dlnb_send(comm, buf, elems(count), dest)); }
+    void recv(void *buf, int count, int source) override { B200_CHECK(dlnb_recv(comm, buf, elems(count), source)); }
+    void Isend(const void *buf, int count, int dest, int index) override {
+        B200_CHECK(dlnb_isend(comm, buf, elems(count), dest, index));
+    }
+    void Irecv(void *buf, int count, int source, int index) override {
+        B200_CHECK(dlnb_irecv(comm, buf, elems(count), source, index));
+    }
+    // Expert-parallel traffic: used only by the MoE hybrid proxy, which is outside this build.
     void Alltoall(const void *, int, void *, int) override { unsupported("Alltoall"); }
-    void send(const void *, int, int) override { unsupported("send"); }
-    void recv(void *, int, int) override { unsupported("recv"); }
-    void Isend(const void *, int, int, int) override { unsupported("Isend"); }
-    void Irecv(void *, int, int, int) override { unsupported("Irecv"); }
 
     // additions
     void set(const char *key, long v) { B200_CHECK(dlnb_comm_set(comm, key, v)); }

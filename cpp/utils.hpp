@@ -3,7 +3,7 @@
 // Same entry points as the reference's cpp/utils.hpp (get_dnnproxy_base_path :44, parse_devices
 // :62, set_local_device :74, estimate_runs :121, compute_msg_stats :145, extract_value :167,
 // get_model_stats :200), written for a build without MPI or nlohmann: cross-rank steps use the
-// C ABI's rendezvous. `count_layers` (:279) belongs to the hybrid proxies and is not built.
+// C ABI's rendezvous. `count_layers` (:279) serves the hybrid proxies.
 #ifndef UTILS_HPP
 #define UTILS_HPP
 
@@ -107,6 +107,25 @@ inline std::map<std::string, uint64_t> get_model_stats(const std::string &filena
         stats[keys[k]] = (k == 4 || k == 5) ? (uint64_t)std::stod(v) : std::stoull(v);
     }
     return stats;
+}
+
+// Number of layers of a model: num_encoder_blocks + num_decoder_blocks of models/<name>.json
+// (reference: count_layers, utils.hpp:279-294, there through nlohmann::json). The files are flat
+// objects of integers, so the two keys are read directly.
+inline unsigned count_layers(const std::string &filename) {
+    std::ifstream in(filename);
+    if (!in.is_open()) throw std::runtime_error("Could not open model architecture file: " + filename);
+    std::stringstream ss;
+    ss << in.rdbuf();
+    const std::string text = ss.str();
+    auto value_of = [&](const std::string &key) -> unsigned {
+        const size_t k = text.find("\"" + key + "\"");
+        if (k == std::string::npos) return 0;
+        const size_t colon = text.find(':', k);
+        if (colon == std::string::npos) return 0;
+        return (unsigned)std::strtoul(text.c_str() + colon + 1, nullptr, 10);
+    };
+    return value_of("num_encoder_blocks") + value_of("num_decoder_blocks");
 }
 
 #endif // UTILS_HPP

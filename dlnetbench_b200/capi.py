@@ -81,6 +81,10 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_allreduce": (i, [vp, vp, vp, sz]),
         "dlnb_allgather": (i, [vp, vp, vp, sz]),
         "dlnb_reduce_scatter": (i, [vp, vp, vp, sz]),
+        "dlnb_send": (i, [vp, vp, sz, i]),
+        "dlnb_recv": (i, [vp, vp, sz, i]),
+        "dlnb_isend": (i, [vp, vp, sz, i, i]),
+        "dlnb_irecv": (i, [vp, vp, sz, i, i]),
         "dlnb_wait": (i, [vp, i]),
         "dlnb_waitall": (i, [vp, i]),
         "dlnb_barrier": (i, [vp]),
@@ -217,6 +221,18 @@ class B200Communicator:
 
     def Reduce_Scatter_block(self, sendbuf, recvbuf, recvcount):
         check(lib().dlnb_reduce_scatter(self.h, sendbuf, recvbuf, recvcount))
+
+    def send(self, buf, count, dest):
+        check(lib().dlnb_send(self.h, buf, count, dest))
+
+    def recv(self, buf, count, source):
+        check(lib().dlnb_recv(self.h, buf, count, source))
+
+    def Isend(self, buf, count, dest, index):
+        check(lib().dlnb_isend(self.h, buf, count, dest, index))
+
+    def Irecv(self, buf, count, source, index):
+        check(lib().dlnb_irecv(self.h, buf, count, source, index))
 
     def Wait(self, index):
         check(lib().dlnb_wait(self.h, index))

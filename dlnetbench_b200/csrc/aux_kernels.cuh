@@ -94,3 +94,99 @@ __global__ void flush_kernel(uint4 *p, size_t nvec, uint32_t tag) {
 }
 
 } // namespace dlnb
+
+// ----------------------------------------------------------------------------
+// Point-to-point put with a rendezvous — ProxyCommunicator::send / recv (reference:
+// cpp/proxy_classes.hpp:103-117 MPI_Send/MPI_Recv, :211-227 ncclSend/ncclRecv), the
+// stage-to-stage traffic of the pipeline proxies (hybrid_2d.cpp:108-161).
+//   recv_post / recv_wait  post the arena offset of the receive buffer into the SENDER's mailbox,
+//                and (separately) wait for the sender's "done" flag;
+//   send_kernel  waits for that post, stores its data straight into the receiver's buffer
+//                (window base of the receiver + posted offset; 128-bit, shifted if needed),
+//                and the last CTA to finish publishes "done" with a system-scope release.
+// The k-th send from a to b matches the k-th recv on b from a (sequence numbers are counted on
+// the host: point-to-point calls are not captured into graphs).
+// ----------------------------------------------------------------------------
+namespace dlnb {
+
+constexpr int P2P_RING = 8; // outstanding receives per (source, destination) pair
+
+struct alignas(128) P2PBox {
+    unsigned long long post[P2P_RING]; // written by the peer as RECEIVER: (arena offset << 16) | (seq & 0xffff), slot seq % 8
+    uint32_t done;                     // written by the peer as SENDER: seq of the last delivered message
+};
+struct P2PState {
+    uint32_t send_ctas_done[MAXR];
+};
+
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// A receive is two tiny kernels. The POST runs in order on the communication stream (whatever
+// used the buffer before is finished) and returns at once. The WAIT is only enqueued when the
+// host asks for completion (Wait / WaitAll / the blocking recv): a kernel that spins on a flag
+// another GPU sets must never sit in front of work that GPU is waiting for — streams may share a
+// hardware queue, and a posted receive followed by a send (ring exchange) would deadlock.
+__global__ void recv_post_kernel(P2PBox *box_at_sender, uint32_t seq, unsigned long long arena_offset) {
+    if (threadIdx.x != 0) return;
+    st_relaxed_sys_u64(&box_at_sender->post[seq % P2P_RING], (arena_offset << 16) | (unsigned long long)(seq & 0xffffu));
+}
+__global__ void recv_wait_kernel(const P2PBox *my_box, uint32_t seq, unsigned long long timeout_ns, uint32_t *host_error) {
+    if (threadIdx.x != 0) return;
+    unsigned long long t0 = 0;
+    unsigned polls = 0;
+    while ((int32_t)(ld_acquire_sys(&my_box->done) - seq) < 0) {
+        if ((++polls & 0x3ff) == 0) {
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > timeout_ns) {
+                if (host_error) *(volatile uint32_t *)host_error = 1;
+                __threadfence_system();
+                break;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(512, 1)
+send_kernel(const P2PBox *my_box, P2PBox *box_at_receiver, char *receiver_window, const void *src, size_t bytes,
+            P2PState *st, int dst, uint32_t seq, unsigned long long timeout_ns, uint32_t *host_error) {
+    __shared__ unsigned long long s_off;
+    if (threadIdx.x == 0) {
+        unsigned long long post, t0 = 0;
+        unsigned polls = 0;
+        while (((post = ld_relaxed_sys_u64(&my_box->post[seq % P2P_RING])) & 0xffffull) != (unsigned long long)(seq & 0xffffu)) {
+            if ((++polls & 0x3ff) == 0) {
+                const unsigned long long now = globaltimer_ns();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > timeout_ns) {
+                    if (host_error) *(volatile uint32_t *)host_error = 1;
+                    __threadfence_system();
+                    break;
+                }
+            }
+        }
+        s_off = post >> 16;
+    }
+    __syncthreads();
+    // payload as 2-byte elements (every dtype here has an even size): pure copy, any alignment
+    const __half *s[1] = {(const __half *)src};
+    __half *d[1] = {(__half *)(receiver_window + s_off)};
+    move_any<__half, 1, 1, 4, 4>(s, d, bytes / 2, blockIdx.x, gridDim.x);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system(); // this CTA's stores are out before it is counted
+        if (atomicAdd(&st->send_ctas_done[dst], 1u) == gridDim.x - 1) {
+            st->send_ctas_done[dst] = 0;
+            st_release_sys(&box_at_receiver->done, seq);
+        }
+    }
+}
+
+} // namespace dlnb

@@ -152,6 +152,9 @@ struct dlnb_comm {
     std::vector<cudaEvent_t> ev_done;          // completion (no timestamp: cheaper), always recorded
     std::vector<char> slot_timed;
     int next_lane = 0;
+    // a posted receive whose completion wait has not been enqueued yet: source world rank and message number
+    std::vector<int> recv_src;
+    std::vector<uint32_t> recv_seq;
     std::vector<char> slot_used;
     long ctas = 0, threads = 512, algo = DLNB_ALGO_AUTO, twoshot_min_bytes = -1 /* auto: 2 MiB / n */, timeout_ms = 30000,
          multimem_min_bytes = 512 << 10;
@@ -170,6 +173,7 @@ struct State {
     // s_comm2 (lane 1) so their barrier latencies overlap; everything else runs on lane 0 alone.
     long lanes = 2;
     cudaEvent_t ev_lane1 = nullptr, ev_excl = nullptr;
+    uint32_t p2p_sent[MAXR] = {}, p2p_posted[MAXR] = {}; // messages sent to / receives posted for each world rank
     bool lane1_dirty = false, excl_pending = false, comm2_in_capture = false;
     cudaEvent_t ev_join = nullptr, ev_copy = nullptr, ev_iter0 = nullptr, ev_iter1 = nullptr, ev_tmp0 = nullptr,
                 ev_tmp1 = nullptr;
@@ -191,6 +195,9 @@ struct State {
     uint32_t *host_error = nullptr, *host_error_dev = nullptr;
     int next_comm = 0;
     std::vector<dlnb_comm *> comms;
+    // point-to-point mailboxes (symmetric, one per peer world rank) and sequence state (local)
+    P2PBox *p2p_boxes = nullptr;
+    P2PState *p2p_state = nullptr;
     // emulation scratch (single-GPU n-rank mode)
     uint32_t *emu_flags = nullptr;
     CommCtl *emu_ctl = nullptr;
@@ -496,6 +503,10 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     G.flag_area = (char *)p;
     if (arena_alloc((size_t)MAX_COMMS * 2 * sizeof(CommCtl), &p)) { G.inited = false; return 1; }
     G.ctl = (CommCtl *)p;
+    if (arena_alloc((size_t)MAXR * sizeof(P2PBox), &p)) { G.inited = false; return 1; }
+    G.p2p_boxes = (P2PBox *)p;
+    CU_TRY(cudaMalloc((void **)&G.p2p_state, sizeof(P2PState)));
+    CU_TRY(cudaMemset(G.p2p_state, 0, sizeof(P2PState)));
     return 0;
 }
 
@@ -541,6 +552,7 @@ extern "C" int dlnb_finalize(void) {
     if (G.emu_ctl) cudaFree(G.emu_ctl);
     if (G.flush_buf) cudaFree(G.flush_buf);
     if (G.d_scalar) cudaFree(G.d_scalar);
+    if (G.p2p_state) cudaFree(G.p2p_state);
     if (G.spin_stamps) cudaFree(G.spin_stamps);
     if (G.host_error) cudaFreeHost(G.host_error);
     cudaStreamDestroy(G.s_compute);
@@ -630,6 +642,8 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
     c->ev_end.resize(c->num_slots + 1);
     c->ev_done.resize(c->num_slots + 1);
     c->slot_timed.assign(c->num_slots + 1, 0);
+    c->recv_src.assign(c->num_slots + 1, -1);
+    c->recv_seq.assign(c->num_slots + 1, 0);
     c->slot_used.assign(c->num_slots + 1, 0);
     for (int i = 0; i <= c->num_slots; ++i) {
         CU_TRY(cudaEventCreate(&c->ev_start[i]));
@@ -944,6 +958,7 @@ extern "C" int dlnb_iallgather(dlnb_comm_t c, const void *send, void *recv, size
 extern "C" int dlnb_ireduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount, int slot) {
     return coll(c, OP_RS, send, recv, recvcount, slot);
 }
+static int finish_recv(dlnb_comm *c, int slot);
 extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
     NEED_INIT();
     if (G.capturing) return 0; // ordering inside a captured iteration is the streams'; the host waits on the replay
@@ -951,6 +966,7 @@ extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
     if (slot == -1) slot = c->num_slots;
     else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
     if (!c->slot_used[slot]) return 0;
+    if (finish_recv(c, slot)) return 1;
     CU_TRY(cudaEventSynchronize(c->ev_done[slot]));
     return check_watchdog();
 }
@@ -961,6 +977,8 @@ extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
     if (nslots > c->num_slots) nslots = c->num_slots;
     // the communication stream is ordered: waiting for the newest used slot suffices,
     // but slots may have been recorded in any order, so wait for each.
+    for (int i = 0; i < nslots; ++i)
+        if (c->slot_used[i] && finish_recv(c, i)) return 1;
     for (int i = 0; i < nslots; ++i)
         if (c->slot_used[i]) CU_TRY(cudaEventSynchronize(c->ev_done[i]));
     return check_watchdog();
@@ -989,10 +1007,89 @@ extern "C" int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms) {
     if (!c || !ms) return fail("null argument");
     if (slot == -1) slot = c->num_slots; // the most recent blocking call
     if (slot < 0 || slot > c->num_slots || !c->slot_used[slot]) return fail("slot %d has no recorded collective", slot);
+    if (c->recv_src[slot] >= 0) return fail("slot %d holds a receive that has not been waited for", slot);
     if (!c->slot_timed[slot]) return fail("slot %d was recorded with slot_timing off", slot);
     CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
     CU_TRY(cudaEventElapsedTime(ms, c->ev_start[slot], c->ev_end[slot]));
     return 0;
+}
+
+// ---------------------------------------------------------------------------
+// point-to-point (pipeline stages): rendezvous put over peer memory
+// ---------------------------------------------------------------------------
+static int p2p(dlnb_comm *c, bool is_send, const void *buf, size_t count, int peer, int slot) {
+    NEED_INIT();
+    if (!c) return fail("null communicator");
+    if (slot == -1) slot = c->num_slots;
+    else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range (communicator has %d)", slot, c->num_slots);
+    if (peer < 0 || peer >= c->n) return fail("peer %d outside the communicator (size %d)", peer, c->n);
+    if (peer == c->me) return fail("send/recv to oneself is not supported");
+    if (G.kind != ARENA_VMM) return fail("send/recv need the VMM arena (one contiguous window per rank)");
+    if (count && !buf) return fail("null buffer");
+    const int wpeer = c->ranks[peer];
+    const size_t bytes = count * dtype_size(c->dtype);
+    const char *b = (const char *)buf;
+    if (count && !(b >= (const char *)G.window[G.rank] && b + bytes <= (const char *)G.window[G.rank] + G.va_used))
+        return fail("buffer %p is not in the symmetric arena (use dlnb_symm_alloc)", buf);
+    if (G.capturing) return fail("send/recv cannot be captured into a graph");
+    if (join_streams()) return 1;
+    if (drain_lane1_into_lane0()) return 1; // ordered on lane 0 behind everything, like allgather / reduce-scatter
+    P2PBox *mine = G.p2p_boxes + wpeer;                                // my box for this peer
+    P2PBox *theirs = (P2PBox *)translate(G.p2p_boxes, wpeer) + G.rank; // the peer's box for me
+    const unsigned long long timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;
+    const bool timed = G.slot_timing != 0;
+    if (timed) CU_TRY(cudaEventRecord(c->ev_start[slot], G.s_comm));
+    if (is_send) {
+        const size_t vecs = bytes / 16 + 1;
+        long g = c->ctas > 0 ? c->ctas : 64;
+        g = std::min<long>(g, std::max<long>(1, (long)((vecs + 511) / 512)));
+        g = std::min<long>(g, G.sms);
+        send_kernel<<<(unsigned)g, 512, 0, G.s_comm>>>(mine, theirs, (char *)G.window[wpeer], buf, bytes, G.p2p_state, wpeer,
+                                                        ++G.p2p_sent[wpeer], timeout_ns, G.host_error_dev);
+        CU_TRY(cudaGetLastError());
+        G.launches++;
+        if (mark_exclusive_on_lane0()) return 1;
+        if (timed) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+        CU_TRY(cudaEventRecord(c->ev_done[slot], G.s_comm));
+        c->recv_src[slot] = -1;
+    } else {
+        const unsigned long long off = (unsigned long long)(b - (const char *)G.window[G.rank]);
+        const uint32_t seq = ++G.p2p_posted[wpeer];
+        recv_post_kernel<<<1, 32, 0, G.s_comm>>>(theirs, seq, off);
+        CU_TRY(cudaGetLastError());
+        G.launches++;
+        if (mark_exclusive_on_lane0()) return 1;
+        // the completion wait is enqueued by dlnb_wait / dlnb_waitall (see recv_wait_kernel)
+        c->recv_src[slot] = wpeer;
+        c->recv_seq[slot] = seq;
+    }
+    c->slot_timed[slot] = timed ? 1 : 0;
+    c->slot_used[slot] = 1;
+    return 0;
+}
+// enqueue the completion wait of a posted receive (if this slot holds one)
+static int finish_recv(dlnb_comm *c, int slot) {
+    if (c->recv_src[slot] < 0) return 0;
+    if (drain_lane1_into_lane0()) return 1;
+    recv_wait_kernel<<<1, 32, 0, G.s_comm>>>(G.p2p_boxes + c->recv_src[slot], c->recv_seq[slot],
+                                             (unsigned long long)c->timeout_ms * 1000000ull, G.host_error_dev);
+    CU_TRY(cudaGetLastError());
+    G.launches++;
+    if (mark_exclusive_on_lane0()) return 1;
+    if (c->slot_timed[slot]) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+    CU_TRY(cudaEventRecord(c->ev_done[slot], G.s_comm));
+    c->recv_src[slot] = -1;
+    return 0;
+}
+extern "C" int dlnb_isend(dlnb_comm_t c, const void *buf, size_t count, int dest, int slot) { return p2p(c, true, buf, count, dest, slot); }
+extern "C" int dlnb_irecv(dlnb_comm_t c, void *buf, size_t count, int source, int slot) { return p2p(c, false, buf, count, source, slot); }
+extern "C" int dlnb_send(dlnb_comm_t c, const void *buf, size_t count, int dest) {
+    if (p2p(c, true, buf, count, dest, -1)) return 1;
+    return dlnb_wait(c, -1);
+}
+extern "C" int dlnb_recv(dlnb_comm_t c, void *buf, size_t count, int source) {
+    if (p2p(c, false, buf, count, source, -1)) return 1;
+    return dlnb_wait(c, -1);
 }
 
 // ---------------------------------------------------------------------------

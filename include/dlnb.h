@@ -137,6 +137,16 @@ int dlnb_allreduce(dlnb_comm_t c, const void *send, void *recv, size_t count);
 int dlnb_allgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount);
 /* ProxyCommunicator::Reduce_Scatter_block (proxy_classes.hpp:38,99-101,206-209): blocking */
 int dlnb_reduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount);
+/* ProxyCommunicator::send / recv / Isend / Irecv (proxy_classes.hpp:45-48,103-117,211-227): the
+ * stage-to-stage traffic of the pipeline proxies (hybrid_2d.cpp:108-161). `dest` / `source` are
+ * ranks of the communicator. The k-th send from a to b matches the k-th recv on b from a (no
+ * tags: the proxies always use 0). A rendezvous put: the receiver posts where its buffer is, the
+ * sender stores straight into it over NVLink. The blocking forms return when the message has
+ * been delivered (send) / has arrived (recv). Needs the VMM arena (world > 1). */
+int dlnb_send(dlnb_comm_t c, const void *buf, size_t count, int dest);
+int dlnb_recv(dlnb_comm_t c, void *buf, size_t count, int source);
+int dlnb_isend(dlnb_comm_t c, const void *buf, size_t count, int dest, int slot);
+int dlnb_irecv(dlnb_comm_t c, void *buf, size_t count, int source, int slot);
 /* ProxyCommunicator::Wait / WaitAll / Barrier (proxy_classes.hpp:41-43,79-89,184-195) */
 int dlnb_wait(dlnb_comm_t c, int slot);
 int dlnb_waitall(dlnb_comm_t c, int nslots);

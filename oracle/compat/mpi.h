@@ -66,11 +66,18 @@ struct alignas(64) BarrierState {
     std::atomic<int> sense;
     char pad[56];
 };
+/* one mailbox per ordered pair of world ranks: blocking Send/Recv hand chunks over through the
+ * sender's staging slot (state 0 = empty, else = bytes of the chunk that is ready) */
+struct alignas(64) Mailbox {
+    std::atomic<uint64_t> ready;
+    char pad[56];
+};
 struct Shared {
     std::atomic<int> next_comm;
     std::atomic<int> abort_flag;
     char pad[56];
     BarrierState bar[MAX_COMMS];
+    Mailbox box[MAX_RANKS][MAX_RANKS]; /* [source][destination] */
     /* followed by MAX_RANKS-many slots of SLOT_BYTES (only world of them are touched) */
 };
 inline size_t shared_bytes(int world) { return sizeof(Shared) + (size_t)world * SLOT_BYTES + 4096; }
@@ -234,6 +241,47 @@ inline void bcast_bytes(char *buf, size_t bytes, int root, Comm *c) {
     }
 }
 
+/* Blocking point-to-point, in order per (source, destination) pair; tags are not needed by
+ * the proxies (always 0). The payload goes through the sender's staging slot in chunks. */
+inline void wait_box(std::atomic<uint64_t> &a, bool want_full) {
+    unsigned spins = 0;
+    while ((a.load(std::memory_order_acquire) != 0) != want_full) {
+        if (++spins > 2000) {
+            sched_yield();
+            if ((spins & 0xffff) == 0 && S().sh->abort_flag.load()) _exit(3);
+        }
+    }
+}
+inline void send_bytes(const char *buf, size_t bytes, int dest, Comm *c) {
+    if (!S().sh) die("MPI_Send with a single rank");
+    const int me = c->world_rank[c->rank], to = c->world_rank[dest];
+    Mailbox &mb = S().sh->box[me][to];
+    size_t base = 0;
+    do {
+        const size_t len = std::min(SLOT_BYTES, bytes - base);
+        wait_box(mb.ready, false);
+        memcpy(slot_in(me), buf + base, len);
+        mb.ready.store(len ? len : (uint64_t)-1, std::memory_order_release); /* zero-length message still signals */
+        base += len;
+    } while (base < bytes);
+    wait_box(mb.ready, false); /* the receiver has copied the last chunk: the slot is free again */
+}
+inline void recv_bytes(char *buf, size_t bytes, int source, Comm *c) {
+    if (!S().sh) die("MPI_Recv with a single rank");
+    const int me = c->world_rank[c->rank], from = c->world_rank[source];
+    Mailbox &mb = S().sh->box[from][me];
+    size_t base = 0;
+    do {
+        wait_box(mb.ready, true);
+        uint64_t len = mb.ready.load(std::memory_order_acquire);
+        if (len == (uint64_t)-1) len = 0;
+        if (base + len > bytes) die("MPI_Recv: message longer than the receive buffer");
+        memcpy(buf + base, slot_in(from), len);
+        mb.ready.store(0, std::memory_order_release);
+        base += len;
+    } while (base < bytes);
+}
+
 inline void run_request(Request *r) {
     switch (r->kind) {
     case REQ_IALLREDUCE: allreduce_f32((const float *)r->send, (float *)r->recv, (size_t)r->count, r->comm); break;
@@ -387,8 +435,14 @@ inline int MPI_Comm_free(MPI_Comm *c) { *c = MPI_COMM_NULL; return MPI_SUCCESS; 
 /* Present in the reference's MPICommunicator but never called by dp / fsdp
  * (SURVEY §2b "never called"): provided so the class compiles; abort if reached. */
 inline int MPI_Alltoall(const void *, int, MPI_Datatype, void *, int, MPI_Datatype, MPI_Comm) { dlnb_mpi::die("MPI_Alltoall not provided"); }
-inline int MPI_Send(const void *, int, MPI_Datatype, int, int, MPI_Comm) { dlnb_mpi::die("MPI_Send not provided"); }
-inline int MPI_Recv(void *, int, MPI_Datatype, int, int, MPI_Comm, MPI_Status *) { dlnb_mpi::die("MPI_Recv not provided"); }
+inline int MPI_Send(const void *b, int count, MPI_Datatype d, int dest, int, MPI_Comm c) {
+    dlnb_mpi::send_bytes((const char *)b, (size_t)count * dlnb_mpi::dt_size(d), dest, c);
+    return MPI_SUCCESS;
+}
+inline int MPI_Recv(void *b, int count, MPI_Datatype d, int source, int, MPI_Comm c, MPI_Status *) {
+    dlnb_mpi::recv_bytes((char *)b, (size_t)count * dlnb_mpi::dt_size(d), source, c);
+    return MPI_SUCCESS;
+}
 inline int MPI_Isend(const void *, int, MPI_Datatype, int, int, MPI_Comm, MPI_Request *) { dlnb_mpi::die("MPI_Isend not provided"); }
 inline int MPI_Irecv(void *, int, MPI_Datatype, int, int, MPI_Comm, MPI_Request *) { dlnb_mpi::die("MPI_Irecv not provided"); }
 

@@ -154,6 +154,20 @@ uint64_t dlnb_oracle_fsdp_lower_bound_us(uint64_t fwd_us, uint64_t bwd_us, int n
     const float f = (float)fwd_us / (float)num_units, b = (float)bwd_us / (float)num_units;
     return (uint64_t)(num_units - 1) * (uint64_t)f + (uint64_t)num_units * (uint64_t)b;
 }
+/* hybrid_2d.cpp:232-250 — GPipe proxy sizing: out[0] = fwd us per micro-batch, out[1] = bwd us per
+ * micro-batch (whole-model time / stages / micro-batches, integer divisions), out[2] = elements of
+ * one stage-to-stage message (seq_len * embed_dim * batch/micro-batches), out[3] = elements of the
+ * per-stage DP allreduce (model size / stages), out[4] = pure-compute critical path of one GPipe
+ * iteration in us: (M + S - 1) * (fwd + bwd). */
+void dlnb_oracle_hybrid2d_sizes(uint64_t fwd_us, uint64_t bwd_us, uint64_t model_size, uint64_t batch, uint64_t seq_len,
+                                uint64_t embed_dim, int num_stages, int num_microbatches, uint64_t *out) {
+    out[0] = fwd_us / (uint64_t)num_stages / (uint64_t)num_microbatches;
+    out[1] = bwd_us / (uint64_t)num_stages / (uint64_t)num_microbatches;
+    out[2] = (uint64_t)((unsigned)seq_len * (unsigned)embed_dim * (batch / (uint64_t)num_microbatches));
+    out[3] = model_size / (uint64_t)num_stages;
+    out[4] = (uint64_t)(num_microbatches + num_stages - 1) * (out[0] + out[1]);
+}
+
 /* utils.hpp:145-159 — mean and population standard deviation, float arithmetic. */
 void dlnb_oracle_msg_stats(const uint64_t *sizes, int n, unsigned mult, float *avg_out, float *std_out) {
     float avg = 0.0f;

@@ -41,6 +41,7 @@ def lib():
         L.dlnb_oracle_dp_lower_bound_us.restype = u64
         L.dlnb_oracle_fsdp_lower_bound_us.argtypes = [u64, u64, i]
         L.dlnb_oracle_fsdp_lower_bound_us.restype = u64
+        L.dlnb_oracle_hybrid2d_sizes.argtypes = [u64, u64, u64, u64, u64, u64, i, i, C.POINTER(u64)]
         L.dlnb_oracle_msg_stats.argtypes = [C.POINTER(u64), i, C.c_uint, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.dlnb_oracle_parse_model_stats.argtypes = [C.c_char_p, C.POINTER(u64)]
         L.dlnb_oracle_pattern_value.argtypes = [i, u64, i, u64]
@@ -101,6 +102,14 @@ def dp_lower_bound_us(fwd, bwd, n):
 
 def fsdp_lower_bound_us(fwd, bwd, u):
     return lib().dlnb_oracle_fsdp_lower_bound_us(fwd, bwd, u)
+
+
+def hybrid2d_sizes(st, num_stages, num_microbatches):
+    """st: parse_model_stats() dict -> fwd/bwd us per micro-batch, pipe message and DP allreduce elements, lower bound us."""
+    out = (C.c_uint64 * 5)()
+    lib().dlnb_oracle_hybrid2d_sizes(st["avgForwardTime"], st["avgBackwardTime"], st["modelSize"], st["batchSize"],
+                                     st["sequenceLength"], st["embeddedDim"], num_stages, num_microbatches, out)
+    return dict(zip(["fwd_us", "bwd_us", "pipe_elems", "dp_elems", "lower_bound_us"], list(out)))
 
 
 def msg_stats(sizes, mult=1):

@@ -66,6 +66,8 @@ def proxies():
         #  sizing rule is the same code path as the two dp cases above)
         ("fsdp", 2, ["llama3_8b_64_bfloat16", "32", "2", ".", "-w", "0", "-r", "1"]),  # C3 at F=2
         ("fsdp", 4, ["gpt2_l_16_bfloat16", "36", "2", ".", "-w", "0", "-r", "1"]),     # HSDP: 2 replicas x F=2
+        ("hybrid_2d", 4, ["vit_b_16_bfloat16", "2", "4", ".", "-w", "0", "-r", "2"]),   # 2 pipelines x 2 stages
+        ("hybrid_2d", 6, ["gpt2_l_16_bfloat16", "3", "8", ".", "-w", "0", "-r", "1"]),  # 2 pipelines x 3 stages (a middle stage)
     ]
     gold = []
     for prog, world, args in runs:
@@ -73,11 +75,12 @@ def proxies():
         print(" ".join(cmd), flush=True)
         res = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True)
         assert res.returncode == 0, res.stderr
-        sec = parse_sections(res.stdout)[prog]
+        sec = parse_sections(res.stdout)["dp_pp" if prog == "hybrid_2d" else prog]
         ranks = sec["ranks"]
         # keep what is deterministic: the global object and the LENGTHS of the per-rank timer lists
         gold.append({"prog": prog, "world": world, "args": args, "global": sec["global"],
-                     "rank_keys": {k: (len(v) if isinstance(v, list) else "scalar") for k, v in ranks["0"].items()}})
+                     "rank_keys": {k: (len(v) if isinstance(v, list) else "scalar") for k, v in ranks["0"].items()},
+                     "rank1_keys": {k: (len(v) if isinstance(v, list) else "scalar") for k, v in ranks.get("1", {}).items()}})
     json.dump(gold, open(os.path.join(OUT, "ref_proxy_outputs.json"), "w"), indent=1)
     print("proxy cases:", len(gold))
 

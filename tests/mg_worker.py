@@ -126,6 +126,33 @@ def main():
         for c in comms.values():
             c.finalize()
 
+    # ---- point-to-point (pipeline stages): ring exchange with Irecv/Isend, then a blocking chain
+    if world > 1:
+        for dtype in (0, 1):
+            comm = capi.B200Communicator(list(range(world)), num_slots=4, dtype=dtype)
+            nxt, prv = (rank + 1) % world, (rank - 1) % world
+            for count in [1, 7, 4097, 65536 + 17, 1_000_003, 8_388_608 + 3]:
+                out, inn = capi.Tensor(count + 8, dtype), capi.Tensor(count + 8, dtype)
+                out.fill(2, 77, rank)
+                for shift in (0, 1, 3):  # shifted buffers: misaligned source and/or destination
+                    inn.fill(0)
+                    comm.Irecv(inn.offset(shift), count, prv, 0)
+                    comm.Isend(out.offset(3 - shift), count, nxt, 1)
+                    comm.WaitAll(2)
+                    bad = capi.verify_sum_pattern(inn.offset(shift), count, 3 - shift, dtype, 2, 77, [prv])
+                    expect(bad == 0, f"send/recv ring dtype={dtype} count={count} shift={shift}: {bad} mismatches")
+            # blocking chain 0 -> 1 -> ... -> n-1 (what a pipeline's forward pass does)
+            count = 2_000_001
+            buf = capi.Tensor(count, dtype)
+            if rank == 0:
+                buf.fill(1, 5, 0)
+            else:
+                comm.recv(buf.data, count, rank - 1)
+            if rank + 1 < world:
+                comm.send(buf.data, count, rank + 1)
+            expect(capi.verify_sum_pattern(buf.data, count, 0, dtype, 1, 5, [0]) == 0, f"send/recv chain dtype={dtype}")
+            comm.finalize()
+
     # ---- a dp-shaped overlapped iteration: spin -> allreduce chains, device-timed
     comm = capi.B200Communicator(list(range(world)), num_slots=8, dtype=capi.F16)
     count = 4_000_001

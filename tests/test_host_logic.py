@@ -112,6 +112,28 @@ def test_driver_cli_matches_reference_conventions(prog, nreq):
     assert res.returncode == 255 and "model stats file does not exist" in res.stderr  # return -1 (dp.cpp:145-148)
 
 
+def test_hybrid_2d_cli_and_argument_checks():
+    exe = os.path.join(ROOT, "bin", "b200", "cpp", "hybrid_parallel", "hybrid_2d")
+    res = subprocess.run([exe, "-h"], capture_output=True, text=True, cwd=ROOT)
+    assert res.returncode == 1 and "num_microbatches" in res.stdout
+    res = subprocess.run([exe, "nope_model", "2", "4", "."], capture_output=True, text=True, cwd=ROOT)
+    assert res.returncode == 255 and "model stats file does not exist" in res.stderr
+    # 36 layers over 5 stages / batch 16 over 3 micro-batches: refused like the reference's asserts (hybrid_2d.cpp:263-267)
+    for args in (["gpt2_l_16_bfloat16", "5", "4", "."], ["gpt2_l_16_bfloat16", "2", "3", "."]):
+        res = subprocess.run([exe, *args], capture_output=True, text=True, cwd=ROOT, env={**os.environ, "DLNB_WORLD": "10", "DLNB_RANK": "0"})
+        assert res.returncode == 1 and "must be multiples" in res.stderr, res.stderr
+
+
+def test_count_layers_reads_the_model_json(tmp_path):
+    src = tmp_path / "t.cpp"
+    src.write_text('#include "utils.hpp"\nint main(int c,char**v){printf("%u\\n",count_layers(v[1]));}\n')
+    exe = tmp_path / "t"
+    subprocess.check_call(["g++", "-std=c++17", "-I" + os.path.join(ROOT, "cpp"), "-I" + os.path.join(ROOT, "include"), "-o", str(exe), str(src),
+                           "-L" + os.path.join(ROOT, "dlnetbench_b200"), "-ldlnb", "-Wl,-rpath," + os.path.join(ROOT, "dlnetbench_b200")])
+    got = {m: int(subprocess.check_output([str(exe), os.path.join(ROOT, "models", m + ".json")])) for m in ("gpt2_l", "vit_b", "llama3_70b", "vit_h")}
+    assert got == {"gpt2_l": 36, "vit_b": 12, "llama3_70b": 80, "vit_h": 32}
+
+
 def test_fsdp_rejects_sharding_factor_not_dividing_world():
     res = subprocess.run([os.path.join(BIN, "fsdp"), "gpt2_l_16_bfloat16", "4", "3", "."], capture_output=True, text=True, cwd=ROOT,
                          env={**os.environ, "DLNB_WORLD": "4", "DLNB_RANK": "0"})

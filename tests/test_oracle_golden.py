@@ -98,8 +98,10 @@ def test_half_and_bf16_conversions_match_numpy(oracle):
 def test_sizing_rules_match_reference_outputs(oracle):
     """Bucket/shard sizes and per-unit times as the reference's own binaries printed them."""
     gold = json.load(open(os.path.join(GOLD, "ref_proxy_outputs.json")))
-    assert {g["prog"] for g in gold} == {"dp", "fsdp"}
+    assert {g["prog"] for g in gold} == {"dp", "fsdp", "hybrid_2d"}
     for g in gold:
+        if g["prog"] == "hybrid_2d":
+            continue  # checked in test_hybrid2d_sizing_matches_reference_outputs
         G = g["global"]
         st = oracle.parse_model_stats(os.path.join(ROOT, "model_stats", g["args"][0] + ".txt"))
         if g["prog"] == "dp":
@@ -126,6 +128,27 @@ def test_sizing_rules_match_reference_outputs(oracle):
             assert rk["allgather_wait_fwd"] == runs * (u - 1) == rk["allgather_wait_bwd"]
             assert rk["barrier"] == (runs if G["num_replicas"] > 1 else 0)
             assert ("allreduce_msg_size_bytes" in G) == (G["num_replicas"] > 1)
+
+
+def test_hybrid2d_sizing_matches_reference_outputs(oracle):
+    """Per-micro-batch times, pipeline message and DP allreduce sizes as the reference's hybrid_2d printed them."""
+    gold = [g for g in json.load(open(os.path.join(GOLD, "ref_proxy_outputs.json"))) if g["prog"] == "hybrid_2d"]
+    assert len(gold) == 2
+    for g in gold:
+        G = g["global"]
+        stages, mbs = int(g["args"][1]), int(g["args"][2])
+        st = oracle.parse_model_stats(os.path.join(ROOT, "model_stats", g["args"][0] + ".txt"))
+        z = oracle.hybrid2d_sizes(st, stages, mbs)
+        assert G["fwd_rt_per_microbatch"] == z["fwd_us"] and G["bwd_rt_per_microbatch"] == z["bwd_us"]
+        assert G["pipe_msg_size_bytes"] == z["pipe_elems"] * 4 and G["dp_allreduce_size_bytes"] == z["dp_elems"] * 4
+        assert G["dp_size"] == g["world"] // stages and G["samples_per_microbatch"] == st["batchSize"] // mbs
+        assert G["global_batch_size"] == g["world"] * st["batchSize"] // stages
+        runs = g["rank_keys"]["runtimes"]
+        # first / last stage time one transfer per micro-batch and direction; a middle stage reports the merged pairs
+        assert g["rank_keys"]["pp_comm_time"] == runs * 2 * mbs and g["rank_keys"]["dp_comm_time"] == runs
+        if stages > 2:
+            assert g["rank1_keys"]["pp_comm_time"] in (2 * mbs, runs * 2 * mbs)
+        assert z["lower_bound_us"] == (mbs + stages - 1) * (z["fwd_us"] + z["bwd_us"])
 
 
 def test_baseline_sizes_and_lower_bounds(oracle):

@@ -16,7 +16,7 @@ from dlnetbench_b200 import capi  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--op", default="allreduce", choices=["allreduce", "allgather", "reduce_scatter"])
+    ap.add_argument("--op", default="allreduce", choices=["allreduce", "allgather", "reduce_scatter", "sendrecv"])
     ap.add_argument("--dtype", default="f16", choices=["f32", "f16", "bf16"])
     ap.add_argument("--min-bytes", type=int, default=1 << 10)
     ap.add_argument("--max-bytes", type=int, default=1 << 30)
@@ -36,11 +36,24 @@ def main():
     comm.set("algo", a.algo)
     comm.set("threads", a.threads)
     # ring of buffers larger than L2 so no iteration finds its input cached
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+
+    def issue(s, r, sc, rc, i):
+        if a.op == "allreduce":
+            comm.Iallreduce(s.data, r.data, sc, i)
+        elif a.op == "allgather":
+            comm.Iallgather(s.data, sc, r.data, sc, i)
+        elif a.op == "reduce_scatter":
+            capi.check(capi.lib().dlnb_ireduce_scatter(comm.h, s.data, r.data, rc, i))
+        else:  # ring exchange: every rank receives from its left and sends to its right
+            comm.Irecv(r.data, rc, prv, i)
+            comm.Isend(s.data, sc, nxt, i)
+
     rows = []
     size = a.min_bytes
     while size <= a.max_bytes:
         count = size // esz
-        if a.op == "allreduce":
+        if a.op in ("allreduce", "sendrecv"):
             sc, rc = count, count
         elif a.op == "allgather":
             sc, rc = count // world, (count // world) * world
@@ -55,13 +68,7 @@ def main():
             comm.set("ctas", ctas)
             for rep in range(2):  # first pass = warm-up
                 for i in range(a.iters):
-                    s, r = send[i % nbuf], recv[i % nbuf]
-                    if a.op == "allreduce":
-                        comm.Iallreduce(s.data, r.data, sc, i)
-                    elif a.op == "allgather":
-                        comm.Iallgather(s.data, sc, r.data, sc, i)
-                    else:
-                        capi.check(capi.lib().dlnb_ireduce_scatter(comm.h, s.data, r.data, rc, i))
+                    issue(send[i % nbuf], recv[i % nbuf], sc, rc, i)
                 comm.WaitAll(a.iters)
             ms = sorted(comm.slot_ms(i) for i in range(a.iters))
             # device-only batch time: a spin blocks the communication stream while the host queues
@@ -70,18 +77,14 @@ def main():
             capi.compute_spin(max(3000.0, 40.0 * a.iters))
             capi.batch_begin()
             for i in range(a.iters):
-                s, r = send[i % nbuf], recv[i % nbuf]
-                if a.op == "allreduce":
-                    comm.Iallreduce(s.data, r.data, sc, i)
-                elif a.op == "allgather":
-                    comm.Iallgather(s.data, sc, r.data, sc, i)
-                else:
-                    capi.check(capi.lib().dlnb_ireduce_scatter(comm.h, s.data, r.data, rc, i))
+                issue(send[i % nbuf], recv[i % nbuf], sc, rc, i)
             b2b = capi.iter_end() / a.iters
             capi.set_option("slot_timing", 1)
             med = b2b if a.b2b else ms[len(ms) // 2]
             if world == 1:
                 bus = 2 * sc * esz / (med * 1e-3) / 1e9
+            elif a.op == "sendrecv":
+                bus = sc * esz / (med * 1e-3) / 1e9  # bytes per direction per GPU
             elif a.op == "allreduce":
                 bus = 2 * (world - 1) / world * sc * esz / (med * 1e-3) / 1e9
             else:
