@@ -127,7 +127,8 @@ def main():
             c.finalize()
 
     # ---- point-to-point (pipeline stages): ring exchange with Irecv/Isend, then a blocking chain
-    if world > 1:
+    # (needs the contiguous VMM windows; the cudaIpc diagnostic arena does not offer send/recv)
+    if world > 1 and capi.lib().dlnb_arena_kind() == b"vmm":
         for dtype in (0, 1):
             comm = capi.B200Communicator(list(range(world)), num_slots=4, dtype=dtype)
             nxt, prv = (rank + 1) % world, (rank - 1) % world
