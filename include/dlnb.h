@@ -142,7 +142,10 @@ int dlnb_reduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recv
  * ranks of the communicator. The k-th send from a to b matches the k-th recv on b from a (no
  * tags: the proxies always use 0). A rendezvous put: the receiver posts where its buffer is, the
  * sender stores straight into it over NVLink. The blocking forms return when the message has
- * been delivered (send) / has arrived (recv). Needs the VMM arena (world > 1). */
+ * been delivered (send) / has arrived (recv). dlnb_irecv only posts the receive; the kernel that
+ * waits for the data is enqueued by dlnb_wait / dlnb_waitall, so a posted receive never sits in
+ * front of a send the peer is waiting for (Irecv + Isend rings are safe). At most 8 receives
+ * from one source may be outstanding. Needs the VMM arena (world > 1); not capturable. */
 int dlnb_send(dlnb_comm_t c, const void *buf, size_t count, int dest);
 int dlnb_recv(dlnb_comm_t c, void *buf, size_t count, int source);
 int dlnb_isend(dlnb_comm_t c, const void *buf, size_t count, int dest, int slot);
