@@ -1218,14 +1218,19 @@ extern "C" int dlnb_graph_destroy(dlnb_graph_t g) {
 // ---------------------------------------------------------------------------
 extern "C" int dlnb_memcpy_h2d(void *dst, const void *src, size_t bytes) {
     NEED_INIT();
-    CU_TRY(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+    // On the communication stream and waited for: a plain cudaMemcpy from pageable memory may
+    // return while the DMA is still in flight, and our streams are non-blocking (they do not
+    // synchronise with the legacy default stream), so a kernel launched next could read stale data.
+    if (drain_lane1_into_lane0()) return 1;
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, G.s_comm));
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
     return 0;
 }
 extern "C" int dlnb_memcpy_d2h(void *dst, const void *src, size_t bytes) {
     NEED_INIT();
-    CU_TRY(cudaStreamSynchronize(G.s_comm2));
+    if (drain_lane1_into_lane0()) return 1;
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, G.s_comm));
     CU_TRY(cudaStreamSynchronize(G.s_comm));
-    CU_TRY(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
     return 0;
 }
 extern "C" int dlnb_memcpy_h2d_async(void *dst, const void *src, size_t bytes) {
