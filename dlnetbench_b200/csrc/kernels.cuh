@@ -2,10 +2,10 @@
 //
 // Kernels here replace the library calls behind the reference's communicator
 // virtuals (cpp/proxy_classes.hpp:66-101 MPI, :149-209 NCCL):
-//   allreduce_oneshot / allreduce_twoshot  <- MPI_Iallreduce / ncclAllReduce (SUM)
-//   allgather_push                         <- MPI_(I)allgather / ncclAllGather
-//   reduce_scatter_pull                    <- MPI_Reduce_scatter_block / ncclReduceScatter
-//   spin_kernel                            <- usleep() compute emulation (dp.cpp:93,98)
+//   allreduce one-shot / fused two-shot / in-switch (multimem)  <- MPI_Iallreduce / ncclAllReduce (SUM)
+//   allgather (push)                                            <- MPI_(I)allgather / ncclAllGather
+//   reduce-scatter (pull)                                       <- MPI_Reduce_scatter_block / ncclReduceScatter
+// (spin kernel, send/recv and the test helpers are in aux_kernels.cuh)
 //
 // All of them address the peers' buffers directly (VMM-mapped peer HBM over
 // NVLink 5 / NVSwitch): 128-bit coalesced loads/stores, fp32 accumulation in fixed

@@ -1,9 +1,10 @@
 // runtime.cu — host side of libdlnb.so: the C ABI declared in include/dlnb.h.
 //
 // One process per GPU. Owns: the rendezvous (bootstrap.cpp), the symmetric arena
-// (cuMem VMM chunks exported as POSIX fds and mapped by every peer), two ordered
-// streams (emulated compute, communication) plus a copy stream, per-slot events,
-// communicators (rank lists + flag rows + control block) and the kernel launches.
+// (cuMem VMM chunks exported as POSIX fds and mapped by every peer, plus their NVSwitch
+// multicast view), the streams (emulated compute, two communication lanes, copies),
+// per-slot events, communicators (rank lists + flag rows + control blocks), the
+// point-to-point mailboxes, CUDA-graph capture of whole iterations and every kernel launch.
 //
 // Reference counterparts: cpp/proxy_classes.hpp (CCLCommunicator :135-253, Tensor
 // :381-444), cpp/utils.hpp:74-117 (set_local_device), cpp/data_parallel/dp.cpp:166-232.
