@@ -168,6 +168,20 @@ void dlnb_oracle_hybrid2d_sizes(uint64_t fwd_us, uint64_t bwd_us, uint64_t model
     out[4] = (uint64_t)(num_microbatches + num_stages - 1) * (out[0] + out[1]);
 }
 
+/* hybrid_3d.cpp:308-323 — the same with T tensor shards: times divided by (micro-batches * T),
+ * out[2] pipe message as above, out[3] = DP allreduce elements = model / (stages * T),
+ * out[4] = compute critical path, out[5] = TP allreduce elements = pipe message / T. */
+void dlnb_oracle_hybrid3d_sizes(uint64_t fwd_us, uint64_t bwd_us, uint64_t model_size, uint64_t batch, uint64_t seq_len,
+                                uint64_t embed_dim, int num_stages, int num_microbatches, int num_tensor_shards, uint64_t *out) {
+    const uint64_t div = (uint64_t)num_microbatches * (uint64_t)num_tensor_shards;
+    out[0] = fwd_us / (uint64_t)num_stages / div;
+    out[1] = bwd_us / (uint64_t)num_stages / div;
+    out[2] = (uint64_t)((unsigned)seq_len * (unsigned)embed_dim * (batch / (uint64_t)num_microbatches));
+    out[3] = model_size / ((uint64_t)num_stages * (uint64_t)num_tensor_shards);
+    out[4] = (uint64_t)(num_microbatches + num_stages - 1) * (out[0] + out[1]);
+    out[5] = out[2] / (uint64_t)num_tensor_shards;
+}
+
 /* utils.hpp:145-159 — mean and population standard deviation, float arithmetic. */
 void dlnb_oracle_msg_stats(const uint64_t *sizes, int n, unsigned mult, float *avg_out, float *std_out) {
     float avg = 0.0f;

@@ -68,6 +68,7 @@ def proxies():
         ("fsdp", 4, ["gpt2_l_16_bfloat16", "36", "2", ".", "-w", "0", "-r", "1"]),     # HSDP: 2 replicas x F=2
         ("hybrid_2d", 4, ["vit_b_16_bfloat16", "2", "4", ".", "-w", "0", "-r", "2"]),   # 2 pipelines x 2 stages
         ("hybrid_2d", 6, ["gpt2_l_16_bfloat16", "3", "8", ".", "-w", "0", "-r", "1"]),  # 2 pipelines x 3 stages (a middle stage)
+        ("hybrid_3d", 8, ["vit_b_16_bfloat16", "2", "4", "2", ".", "-w", "0", "-r", "1"]),  # 2 replicas x 2 stages x 2 shards
     ]
     gold = []
     for prog, world, args in runs:
@@ -75,7 +76,7 @@ def proxies():
         print(" ".join(cmd), flush=True)
         res = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True)
         assert res.returncode == 0, res.stderr
-        sec = parse_sections(res.stdout)["dp_pp" if prog == "hybrid_2d" else prog]
+        sec = parse_sections(res.stdout)[{"hybrid_2d": "dp_pp", "hybrid_3d": "dp_pp_tp"}.get(prog, prog)]
         ranks = sec["ranks"]
         # keep what is deterministic: the global object and the LENGTHS of the per-rank timer lists
         gold.append({"prog": prog, "world": world, "args": args, "global": sec["global"],

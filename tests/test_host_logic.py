@@ -124,6 +124,17 @@ def test_hybrid_2d_cli_and_argument_checks():
         assert res.returncode == 1 and "must be multiples" in res.stderr, res.stderr
 
 
+def test_hybrid_3d_cli_and_argument_checks():
+    exe = os.path.join(ROOT, "bin", "b200", "cpp", "hybrid_parallel", "hybrid_3d")
+    res = subprocess.run([exe, "-h"], capture_output=True, text=True, cwd=ROOT)
+    assert res.returncode == 1 and "num_tensor_shards" in res.stdout
+    res = subprocess.run([exe, "gpt2_l_16_bfloat16", "2", "4", "."], capture_output=True, text=True, cwd=ROOT)  # one short
+    assert res.returncode == 1 and "Usage" in res.stdout
+    res = subprocess.run([exe, "gpt2_l_16_bfloat16", "2", "4", "3", "."], capture_output=True, text=True, cwd=ROOT,
+                         env={**os.environ, "DLNB_WORLD": "8", "DLNB_RANK": "0"})  # 8 ranks over 2 x 3
+    assert res.returncode == 1 and "stages x tensor shards" in res.stderr
+
+
 def test_count_layers_reads_the_model_json(tmp_path):
     src = tmp_path / "t.cpp"
     src.write_text('#include "utils.hpp"\nint main(int c,char**v){printf("%u\\n",count_layers(v[1]));}\n')

@@ -43,7 +43,9 @@ def test_ipc_arena_fallback_on_2_gpus():
     ("data_parallel/dp", ["gpt2_l_16_bfloat16", "10", ".", "-t", "fp32", "-r", "3"], "dp"),
     ("data_parallel/dp", ["gpt2_l_16_bfloat16", "100", ".", "-t", "fp32", "-r", "3", "-g"], "dp"),
     ("data_parallel/fsdp", ["gpt2_l_16_bfloat16", "36", "2", ".", "-t", "fp16", "-r", "2"], "fsdp"),
-    ("hybrid_parallel/hybrid_2d", ["gpt2_l_16_bfloat16", "2", "4", ".", "-t", "fp16", "-r", "3"], "dp_pp")])
+    ("hybrid_parallel/hybrid_2d", ["gpt2_l_16_bfloat16", "2", "4", ".", "-t", "fp16", "-r", "3"], "dp_pp"),
+    # one stage, two tensor shards: compute + the four tensor-parallel allreduces per micro-batch
+    ("hybrid_parallel/hybrid_3d", ["gpt2_l_16_bfloat16", "1", "4", "2", ".", "-t", "fp16", "-r", "3"], "dp_pp_tp")])
 def test_proxy_binaries_on_2_gpus(prog, args, section):
     if GPU_COUNT < 2:
         pytest.skip("needs 2 GPUs")
@@ -58,6 +60,22 @@ def test_proxy_binaries_on_2_gpus(prog, args, section):
     assert g["backend"] == "B200P2P" and g["world_size"] == 2 and sorted(sec["rank_outputs"]) == [0, 1]
     # emulated compute dominates these configurations: the device-timed iteration stays near its lower bound
     assert 1.0 <= g["ratio_to_lower_bound"] < 1.25, g["ratio_to_lower_bound"]
+
+
+def test_hybrid_3d_on_4_gpus_two_stages_two_shards():
+    if GPU_COUNT < 4:
+        pytest.skip("needs 4 GPUs")
+    from dlnetbench_b200.parser import parse_sections
+
+    res = subprocess.run([os.path.join(ROOT, "bin", "dlnb_launch"), "-n", "4",
+                          os.path.join(ROOT, "bin", "b200", "cpp", "hybrid_parallel", "hybrid_3d"),
+                          "gpt2_l_16_bfloat16", "2", "4", "2", ".", "-t", "fp16", "-r", "3"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    sec = parse_sections(res.stdout)["dp_pp_tp"]
+    ro = sec["rank_outputs"]
+    assert [(ro[r]["stage_id"], ro[r]["tp_id"], ro[r]["dp_id"]) for r in range(4)] == [(0, 0, 0), (0, 1, 0), (1, 0, 0), (1, 1, 0)]
+    assert len(ro[0]["tp_comm_time"]) == 3 * 4 * 4 and sec["json_data"]["dp_size"] == 1
 
 
 def test_hybrid_2d_on_4_gpus_two_pipelines():

@@ -98,9 +98,9 @@ def test_half_and_bf16_conversions_match_numpy(oracle):
 def test_sizing_rules_match_reference_outputs(oracle):
     """Bucket/shard sizes and per-unit times as the reference's own binaries printed them."""
     gold = json.load(open(os.path.join(GOLD, "ref_proxy_outputs.json")))
-    assert {g["prog"] for g in gold} == {"dp", "fsdp", "hybrid_2d"}
+    assert {g["prog"] for g in gold} == {"dp", "fsdp", "hybrid_2d", "hybrid_3d"}
     for g in gold:
-        if g["prog"] == "hybrid_2d":
+        if g["prog"].startswith("hybrid"):
             continue  # checked in test_hybrid2d_sizing_matches_reference_outputs
         G = g["global"]
         st = oracle.parse_model_stats(os.path.join(ROOT, "model_stats", g["args"][0] + ".txt"))
@@ -149,6 +149,23 @@ def test_hybrid2d_sizing_matches_reference_outputs(oracle):
         if stages > 2:
             assert g["rank1_keys"]["pp_comm_time"] in (2 * mbs, runs * 2 * mbs)
         assert z["lower_bound_us"] == (mbs + stages - 1) * (z["fwd_us"] + z["bwd_us"])
+
+
+def test_hybrid3d_sizing_matches_reference_outputs(oracle):
+    gold = [g for g in json.load(open(os.path.join(GOLD, "ref_proxy_outputs.json"))) if g["prog"] == "hybrid_3d"]
+    assert len(gold) == 1
+    for g in gold:
+        G = g["global"]
+        stages, mbs, tp = int(g["args"][1]), int(g["args"][2]), int(g["args"][3])
+        st = oracle.parse_model_stats(os.path.join(ROOT, "model_stats", g["args"][0] + ".txt"))
+        z = oracle.hybrid3d_sizes(st, stages, mbs, tp)
+        assert G["fwd_rt_per_microbatch"] == z["fwd_us"] and G["bwd_rt_per_microbatch"] == z["bwd_us"]
+        assert G["pipe_msg_size_bytes"] == z["pipe_elems"] * 4 and G["tp_allreduce_size_bytes"] == z["tp_elems"] * 4
+        assert G["dp_allreduce_size_bytes"] == z["dp_elems"] * 4 and G["dp_size"] == g["world"] // (stages * tp)
+        assert G["global_batch_size"] == G["dp_size"] * st["batchSize"]
+        runs = g["rank_keys"]["runtimes"]
+        assert g["rank_keys"]["tp_comm_time"] == runs * 4 * mbs and g["rank_keys"]["dp_comm_time"] == runs
+        assert set(g["rank_keys"]) >= {"stage_id", "tp_id", "dp_id", "pp_comm_time"}
 
 
 def test_baseline_sizes_and_lower_bounds(oracle):
