@@ -96,8 +96,11 @@ class B200Communicator : public ProxyCommunicator {
     void Irecv(void *buf, int count, int source, int index) override {
         B200_CHECK(dlnb_irecv(comm, buf, elems(count), source, index));
     }
-    // Expert-parallel traffic: used only by the MoE hybrid proxy, which is outside this build.
-    void Alltoall(const void *, int, void *, int) override { unsupported("Alltoall"); }
+    // Expert-parallel token exchange of the MoE proxy.
+    void Alltoall(const void *sendbuf, int sendcount, void *recvbuf, int recvcount) override {
+        same(sendcount, recvcount);
+        B200_CHECK(dlnb_alltoall(comm, sendbuf, recvbuf, elems(sendcount)));
+    }
 
     // additions
     void set(const char *key, long v) { B200_CHECK(dlnb_comm_set(comm, key, v)); }
@@ -121,13 +124,9 @@ class B200Communicator : public ProxyCommunicator {
     }
     static void same(int a, int b) {
         if (a != b) {
-            fprintf(stderr, "[rank %d] allgather with sendcount %d != recvcount %d is not supported\n", dlnb_rank(), a, b);
+            fprintf(stderr, "[rank %d] sendcount %d != recvcount %d is not supported\n", dlnb_rank(), a, b);
             _exit(1);
         }
-    }
-    [[noreturn]] static void unsupported(const char *what) {
-        fprintf(stderr, "[rank %d] B200Communicator::%s is not part of the data-parallel build\n", dlnb_rank(), what);
-        _exit(1);
     }
     dlnb_comm_t comm = nullptr;
     int comm_size = 1;

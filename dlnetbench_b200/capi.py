@@ -81,6 +81,9 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_allreduce": (i, [vp, vp, vp, sz]),
         "dlnb_allgather": (i, [vp, vp, vp, sz]),
         "dlnb_reduce_scatter": (i, [vp, vp, vp, sz]),
+        "dlnb_alltoall": (i, [vp, vp, vp, sz]),
+        "dlnb_ialltoall": (i, [vp, vp, vp, sz, i]),
+        "dlnb_emu_alltoall": (i, [i, pvp, pvp, sz, i, i]),
         "dlnb_send": (i, [vp, vp, sz, i]),
         "dlnb_recv": (i, [vp, vp, sz, i]),
         "dlnb_isend": (i, [vp, vp, sz, i, i]),
@@ -222,6 +225,10 @@ class B200Communicator:
     def Reduce_Scatter_block(self, sendbuf, recvbuf, recvcount):
         check(lib().dlnb_reduce_scatter(self.h, sendbuf, recvbuf, recvcount))
 
+    def Alltoall(self, sendbuf, sendcount, recvbuf, recvcount):
+        assert sendcount == recvcount
+        check(lib().dlnb_alltoall(self.h, sendbuf, recvbuf, sendcount))
+
     def send(self, buf, count, dest):
         check(lib().dlnb_send(self.h, buf, count, dest))
 
@@ -332,6 +339,10 @@ def emu_allreduce_noalloc(send_ptrs, recv_ptrs, count, dtype, algo=ALGO_AUTO, ct
 
 def emu_allgather(send_ptrs, recv_ptrs, sendcount, dtype, ctas=0):
     check(lib().dlnb_emu_allgather(len(send_ptrs), _ptr_array(send_ptrs), _ptr_array(recv_ptrs), sendcount, dtype, ctas))
+
+
+def emu_alltoall(send_ptrs, recv_ptrs, sendcount, dtype, ctas=0):
+    check(lib().dlnb_emu_alltoall(len(send_ptrs), _ptr_array(send_ptrs), _ptr_array(recv_ptrs), sendcount, dtype, ctas))
 
 
 def emu_reduce_scatter(send_ptrs, recv_ptrs, recvcount, dtype, ctas=0):

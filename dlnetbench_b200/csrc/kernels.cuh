@@ -568,6 +568,29 @@ __device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t re
 }
 
 // ----------------------------------------------------------------------------
+// All-to-all, push: block p of my send buffer (sendcount elements at p*sendcount) goes into
+// slot `rank` of rank p's recv — ProxyCommunicator::Alltoall (cpp/proxy_classes.hpp:74-77 MPI_Alltoall,
+// :160-182 grouped ncclSend/ncclRecv), the expert-parallel token exchange of hybrid_3d_moe.cpp:161-165.
+// Peers are visited starting from my right-hand neighbour so the n ranks do not all hit the same
+// destination at once. Wire: (n-1)*sendcount per direction.
+// ----------------------------------------------------------------------------
+template <typename T, int NR>
+__device__ __forceinline__ void alltoall_body(const RankView &v, size_t sendcount, int cta, int nctas) {
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
+
+    for (int k = 0; k < NR; ++k) {
+        const int p = (v.rank + 1 + k) % NR;
+        const T *src[1] = {(const T *)v.send[v.rank] + (size_t)p * sendcount};
+        T *dst[1] = {(T *)v.recv[p] + (size_t)v.rank * sendcount};
+        move_any<T, 1, 1, 4, 4>(src, dst, sendcount, cta, nctas);
+    }
+
+    cta_barrier<true>(v, e + 2, cta); // publishes the pushed blocks
+    cta_finish(v, e + 2, cta);
+}
+
+// ----------------------------------------------------------------------------
 // Allreduce through NVSwitch multicast ("NVLS"): rank r owns slice r as in the two-shot
 // kernel, but ONE multimem.ld_reduce fetches the slice from all ranks and has the switch add
 // them (fp32 accumulation), and ONE multimem.st writes the result into every rank's recv.
@@ -659,7 +682,7 @@ __device__ __forceinline__ void allreduce_multimem_body(const RankView &v, size_
 // __global__ wrappers. Real mode: one rank per GPU, gridDim.y == 1. Emulation
 // mode: gridDim.y virtual ranks on one GPU in one cooperative launch.
 // ----------------------------------------------------------------------------
-enum Op { OP_AR1 = 0, OP_AR2 = 1, OP_AG = 2, OP_RS = 3, OP_ARM = 4 };
+enum Op { OP_AR1 = 0, OP_AR2 = 1, OP_AG = 2, OP_RS = 3, OP_ARM = 4, OP_A2A = 5 };
 
 template <typename T, int NR, int OP>
 __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta, int nctas) {
@@ -667,6 +690,7 @@ __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta,
     else if (OP == OP_AR2) allreduce_twoshot_body<T, NR>(v, count, cta, nctas);
     else if (OP == OP_AG) allgather_body<T, NR>(v, count, cta, nctas);
     else if (OP == OP_ARM) allreduce_multimem_body<T, NR>(v, count, cta, nctas);
+    else if (OP == OP_A2A) alltoall_body<T, NR>(v, count, cta, nctas);
     else reduce_scatter_body<T, NR>(v, count, cta, nctas);
 }
 

@@ -779,6 +779,7 @@ static size_t work_bytes(int op, int n, size_t count, size_t esz) {
     case OP_AR1: return count * esz;
     case OP_AR2: return count * esz / (size_t)n;
     case OP_ARM: return count * esz / (size_t)n;
+    case OP_A2A: return count * esz; // one block per peer, walked one after the other
     case OP_AG: return count * esz;
     default: return count * esz;
     }
@@ -958,6 +959,13 @@ extern "C" int dlnb_iallgather(dlnb_comm_t c, const void *send, void *recv, size
 }
 extern "C" int dlnb_ireduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount, int slot) {
     return coll(c, OP_RS, send, recv, recvcount, slot);
+}
+extern "C" int dlnb_ialltoall(dlnb_comm_t c, const void *send, void *recv, size_t sendcount, int slot) {
+    return coll(c, OP_A2A, send, recv, sendcount, slot);
+}
+extern "C" int dlnb_alltoall(dlnb_comm_t c, const void *send, void *recv, size_t sendcount) {
+    if (coll(c, OP_A2A, send, recv, sendcount, -1)) return 1;
+    return dlnb_wait(c, -1);
 }
 static int finish_recv(dlnb_comm *c, int slot);
 extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
@@ -1403,6 +1411,10 @@ extern "C" int dlnb_emu_allgather(int nranks, const void *const *send, void *con
 extern "C" int dlnb_emu_reduce_scatter(int nranks, const void *const *send, void *const *recv, size_t recvcount,
                                        int dtype, int ctas) {
     return emu(OP_RS, nranks, send, recv, recvcount, dtype, ctas);
+}
+extern "C" int dlnb_emu_alltoall(int nranks, const void *const *send, void *const *recv, size_t sendcount, int dtype,
+                                 int ctas) {
+    return emu(OP_A2A, nranks, send, recv, sendcount, dtype, ctas);
 }
 
 // ---------------------------------------------------------------------------

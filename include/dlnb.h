@@ -137,6 +137,11 @@ int dlnb_allreduce(dlnb_comm_t c, const void *send, void *recv, size_t count);
 int dlnb_allgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount);
 /* ProxyCommunicator::Reduce_Scatter_block (proxy_classes.hpp:38,99-101,206-209): blocking */
 int dlnb_reduce_scatter(dlnb_comm_t c, const void *send, void *recv, size_t recvcount);
+/* ProxyCommunicator::Alltoall (proxy_classes.hpp:39-40,74-77,160-182): block p of `send`
+ * (sendcount elements at p*sendcount) lands in block `rank` of rank p's `recv`; recvcount ==
+ * sendcount. The expert-parallel token exchange of the MoE proxy (hybrid_3d_moe.cpp:161-165). */
+int dlnb_alltoall(dlnb_comm_t c, const void *send, void *recv, size_t sendcount);
+int dlnb_ialltoall(dlnb_comm_t c, const void *send, void *recv, size_t sendcount, int slot);
 /* ProxyCommunicator::send / recv / Isend / Irecv (proxy_classes.hpp:45-48,103-117,211-227): the
  * stage-to-stage traffic of the pipeline proxies (hybrid_2d.cpp:108-161). `dest` / `source` are
  * ranks of the communicator. The k-th send from a to b matches the k-th recv on b from a (no
@@ -215,6 +220,8 @@ int dlnb_emu_allgather(int nranks, const void *const *send, void *const *recv, s
                        int dtype, int ctas);
 int dlnb_emu_reduce_scatter(int nranks, const void *const *send, void *const *recv,
                             size_t recvcount, int dtype, int ctas);
+int dlnb_emu_alltoall(int nranks, const void *const *send, void *const *recv, size_t sendcount,
+                      int dtype, int ctas);
 
 /* ---- the emulated allreduce for callers that cannot allocate -----------------------
  * No counterpart in the reference (it has no such constraint: every backend there allocates

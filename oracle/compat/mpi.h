@@ -230,6 +230,25 @@ inline void reduce_scatter_block_f32(const float *send, float *recv, size_t recv
     }
 }
 
+/* block d of my send buffer goes to rank d; I receive block `me` of everybody's, in rank order */
+inline void alltoall_bytes(const char *send, size_t bbytes, char *recv, Comm *c) {
+    if (c->size == 1) {
+        if (recv != send) memcpy(recv, send, bbytes);
+        return;
+    }
+    const int n = c->size, me = c->rank;
+    const size_t CH = SLOT_BYTES / (size_t)n; /* bytes per destination per round */
+    for (size_t base = 0; base < bbytes || base == 0; base += CH) {
+        const size_t len = std::min(CH, bbytes - base);
+        char *mine = slot_in(c->world_rank[me]);
+        for (int d = 0; d < n; ++d) memcpy(mine + (size_t)d * CH, send + (size_t)d * bbytes + base, len);
+        barrier(c);
+        for (int r = 0; r < n; ++r) memcpy(recv + (size_t)r * bbytes + base, slot_in(c->world_rank[r]) + (size_t)me * CH, len);
+        barrier(c);
+        if (bbytes == 0) break;
+    }
+}
+
 inline void bcast_bytes(char *buf, size_t bytes, int root, Comm *c) {
     if (c->size == 1) return;
     for (size_t base = 0; base < bytes; base += SLOT_BYTES) {
@@ -434,7 +453,10 @@ inline int MPI_Comm_free(MPI_Comm *c) { *c = MPI_COMM_NULL; return MPI_SUCCESS; 
 
 /* Present in the reference's MPICommunicator but never called by dp / fsdp
  * (SURVEY §2b "never called"): provided so the class compiles; abort if reached. */
-inline int MPI_Alltoall(const void *, int, MPI_Datatype, void *, int, MPI_Datatype, MPI_Comm) { dlnb_mpi::die("MPI_Alltoall not provided"); }
+inline int MPI_Alltoall(const void *s, int sc, MPI_Datatype sd, void *r, int, MPI_Datatype, MPI_Comm c) {
+    dlnb_mpi::alltoall_bytes((const char *)s, (size_t)sc * dlnb_mpi::dt_size(sd), (char *)r, c);
+    return MPI_SUCCESS;
+}
 inline int MPI_Send(const void *b, int count, MPI_Datatype d, int dest, int, MPI_Comm c) {
     dlnb_mpi::send_bytes((const char *)b, (size_t)count * dlnb_mpi::dt_size(d), dest, c);
     return MPI_SUCCESS;

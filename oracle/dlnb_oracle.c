@@ -129,6 +129,13 @@ void dlnb_oracle_reduce_scatter_block(const void *const *send, int nranks, int m
     }
 }
 
+/* MPICommunicator::Alltoall (cpp/proxy_classes.hpp:74-77): send[r] holds nranks blocks of `count`
+ * elements; rank `me` receives block `me` of every rank's send buffer, in rank order. */
+void dlnb_oracle_alltoall(const void *const *send, int nranks, int me, void *recv, size_t count, int dtype) {
+    const size_t b = count * esize(dtype);
+    for (int r = 0; r < nranks; ++r) memcpy((char *)recv + (size_t)r * b, (const char *)send[r] + (size_t)me * b, b);
+}
+
 /* ---- sizing rules -----------------------------------------------------------------
  * dp.cpp:159-164 — bucket i gets floor(M/N) + (i < M mod N). */
 void dlnb_oracle_bucket_sizes(uint64_t model_size, int num_buckets, uint64_t *out) {

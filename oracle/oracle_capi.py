@@ -35,6 +35,7 @@ def lib():
         L.dlnb_oracle_allreduce.argtypes = [pvp, i, vp, sz, i]
         L.dlnb_oracle_allgather.argtypes = [pvp, i, vp, sz, i]
         L.dlnb_oracle_reduce_scatter_block.argtypes = [pvp, i, i, vp, sz, i]
+        L.dlnb_oracle_alltoall.argtypes = [pvp, i, i, vp, sz, i]
         L.dlnb_oracle_bucket_sizes.argtypes = [u64, i, C.POINTER(u64)]
         L.dlnb_oracle_shard_sizes.argtypes = [u64, i, i, C.POINTER(u64)]
         L.dlnb_oracle_dp_lower_bound_us.argtypes = [u64, u64, i]
@@ -82,6 +83,12 @@ def allgather(send, dtype):
 def reduce_scatter_block(send, me, recvcount, dtype):
     out = np.empty(recvcount, dtype=send[0].dtype)
     lib().dlnb_oracle_reduce_scatter_block(_ptrs(send), len(send), me, out.ctypes.data, recvcount, dtype)
+    return out
+
+
+def alltoall(send, me, count, dtype):
+    out = np.empty(count * len(send), dtype=send[0].dtype)
+    lib().dlnb_oracle_alltoall(_ptrs(send), len(send), me, out.ctypes.data, count, dtype)
     return out
 
 

@@ -6,7 +6,7 @@
 // rank's receive buffer to <prefix>.r<rank>.bin (raw fp32 — the MPI path is fp32-only,
 // proxy_classes.hpp:67,71,100).
 //
-//   dlnb_mpirun -n K ref_collectives <allreduce|iallreduce|allgather|iallgather|reduce_scatter>
+//   dlnb_mpirun -n K ref_collectives <allreduce|iallreduce|allgather|iallgather|reduce_scatter|alltoall>
 //                                   <count> <kind> <seed> <prefix>
 #include <mpi.h>
 
@@ -57,6 +57,7 @@ int main(int argc, char **argv) {
     uint64_t send_n = count, recv_n = count;
     if (op == "allgather" || op == "iallgather") recv_n = count * size;
     if (op == "reduce_scatter") send_n = count * size;
+    if (op == "alltoall") { send_n = count * size; recv_n = count * size; }
     Tensor<float, Device::CPU> send(send_n ? send_n : 1), recv(recv_n ? recv_n : 1);
     for (uint64_t i = 0; i < send_n; ++i) send.data[i] = pattern_value(kind, seed, rank, i);
 
@@ -65,6 +66,7 @@ int main(int argc, char **argv) {
     else if (op == "allgather") comm->Allgather(send.data, (int)count, recv.data, (int)count);
     else if (op == "iallgather") { comm->Iallgather(send.data, (int)count, recv.data, (int)count, 1); comm->Wait(1); }
     else if (op == "reduce_scatter") comm->Reduce_Scatter_block(send.data, recv.data, (int)count);
+    else if (op == "alltoall") comm->Alltoall(send.data, (int)count, recv.data, (int)count);
     else { if (!rank) fprintf(stderr, "unknown op %s\n", op.c_str()); MPI_Finalize(); return 2; }
 
     const std::string path = prefix + ".r" + std::to_string(rank) + ".bin";

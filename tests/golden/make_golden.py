@@ -30,9 +30,9 @@ def run_collective(op, world, count, kind, seed):
 def collectives():
     cases = {}
     for world in (1, 2, 3, 4, 8):
-        for op in ("iallreduce", "allreduce", "iallgather", "reduce_scatter"):
+        for op in ("iallreduce", "allreduce", "iallgather", "reduce_scatter", "alltoall"):
             for kind in (1, 2):
-                for count in (1, 7, 4097):
+                for count in ((1, 7, 513) if op == "alltoall" else (1, 7, 4097)):
                     outs = run_collective(op, world, count, kind, 1234)
                     key = f"{op}_w{world}_k{kind}_c{count}"
                     if op in ("iallreduce", "allreduce", "iallgather"):

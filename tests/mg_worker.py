@@ -98,6 +98,14 @@ def main():
                     for r in range(n):
                         bad = capi.verify_sum_pattern(gathered.offset(r * count), count, 0, dtype, kind, seed, [g[r]])
                         expect(bad == 0, f"allgather {gname} dtype={dtype} count={count} block={r}: {bad} mismatches")
+                    # ---- all-to-all: block p of the result must be block `me` of rank g[p]'s pattern
+                    if count <= 1_000_003:
+                        a2a_send, a2a_recv = capi.Tensor(count * n, dtype), capi.Tensor(count * n, dtype)
+                        a2a_send.fill(kind, seed, rank)
+                        comm.Alltoall(a2a_send.data, count, a2a_recv.data, count)
+                        for r in range(n):
+                            bad = capi.verify_sum_pattern(a2a_recv.offset(r * count), count, me * count, dtype, kind, seed, [g[r]])
+                            expect(bad == 0, f"alltoall {gname} dtype={dtype} count={count} block={r}: {bad} mismatches")
                     # ---- reduce-scatter of the gathered buffer's shape: send n*count, receive block `me`
                     rs_send, rs_recv = capi.Tensor(count * n, dtype), capi.Tensor(count, dtype)
                     rs_send.fill(kind, seed, rank)

@@ -92,6 +92,19 @@ def test_emu_reduce_scatter_matches_oracle(dl, oracle, n, dtype):
                 assert np.array_equal(bits(recv[r].download(NPDT[dtype])), bits(want)), (n, dtype, kind, count, r)
 
 
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("n", [2, 3, 8])
+def test_emu_alltoall_matches_oracle(dl, oracle, n, dtype):
+    for count in EDGE_COUNTS[:-1] + [300_001]:  # odd counts: misaligned blocks on both sides
+        xs = host_inputs(oracle, n, count * n, dtype, 2)
+        send = make_dev(dl, xs, dtype)
+        recv = [dl.Tensor(count * n, dtype) for _ in range(n)]
+        dl.emu_alltoall([t.data for t in send], [t.data for t in recv], count, dtype, ctas=4)
+        for r in range(n):
+            want = oracle.alltoall(xs, r, count, dtype)
+            assert np.array_equal(bits(recv[r].download(NPDT[dtype])), bits(want)), (n, dtype, count, r)
+
+
 def test_emu_allreduce_many_ctas_and_repeats(dl, oracle):
     """Flag generations stay consistent across back-to-back launches with different grids."""
     n, dtype, count = 8, 1, 3_000_001

@@ -21,8 +21,8 @@ def gold():
 
 def test_golden_file_covers_every_collective(gold):
     ops = {k.split("_w")[0] for k in gold.files}
-    assert ops == {"iallreduce", "allreduce", "iallgather", "reduce_scatter"}
-    assert len(gold.files) == 5 * 4 * 2 * 3
+    assert ops == {"iallreduce", "allreduce", "iallgather", "reduce_scatter", "alltoall"}
+    assert len(gold.files) == 5 * 5 * 2 * 3
 
 
 def _case(key):
@@ -40,6 +40,9 @@ def test_oracle_reproduces_reference_collectives_bit_for_bit(oracle, gold):
         elif op == "iallgather":
             xs = [oracle.fill_pattern(count, 0, kind, 1234, r) for r in range(world)]
             got = oracle.allgather(xs, 0)
+        elif op == "alltoall":
+            xs = [oracle.fill_pattern(count * world, 0, kind, 1234, r) for r in range(world)]
+            got = np.concatenate([oracle.alltoall(xs, r, count, 0) for r in range(world)])
         else:
             xs = [oracle.fill_pattern(count * world, 0, kind, 1234, r) for r in range(world)]
             got = np.concatenate([oracle.reduce_scatter_block(xs, r, count, 0) for r in range(world)])
