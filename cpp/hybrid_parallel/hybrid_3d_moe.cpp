@@ -1,0 +1,311 @@
+// hybrid_3d_moe / hybrid_3d_moe_loop — data + pipeline + expert parallel (MoE) training proxy, b200 build.
+//
+// Same CLI, inputs and output section as the reference's cpp/hybrid_parallel/hybrid_3d_moe.cpp
+// (`hybrid_3d_moe <model> <num_stages> <num_microbatches> <num_expert_shards> <base_path> [-w][-r][-d][-m][-h]`,
+// section "dp_pp_ep" with the keys of hybrid_3d_moe.cpp:564-595). World rank r = (dp * S + stage) * E + ep
+// (:313-315). Per micro-batch and direction the E ranks of an expert group exchange tokens with
+// 2 * layers_per_stage all-to-alls (:161-165,196-200); at the end they allreduce the non-expert gradients and
+// the ranks with equal (stage, ep) allreduce all gradients (:202-208). Pipelines run GPipe with blocking
+// send / recv as in hybrid_2d.
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+#include <vector>
+
+#include "../data_types.hpp"
+#include "../netcommunicators.hpp"
+#include "../proxy_classes.hpp"
+#include "../utils.hpp"
+
+constexpr Device device = Device::GPU;
+
+static b200::HostTimer timer_runtime, timer_pp_comm, timer_dp_comm, timer_ep_comm, timer_dp_ep_comm;
+
+static inline void emulate_compute(uint64_t usec) { b200::check(dlnb_compute_spin((double)usec), "compute spin"); }
+
+// One GPipe iteration: all micro-batches forward, then all backward, then the DP allreduce.
+template <typename T>
+int run_data_pipe_expert_parallel(int num_microbatches, int stage_id, int num_stage, int layers_per_stage,
+                                  uint64_t pipe_msg_size, uint64_t fwd_rt, uint64_t bwd_rt, Tensor<T, device> *grad_ptr,
+                                  Tensor<T, device> *sum_grad_ptr, uint64_t dp_allreduce_size, uint64_t non_expert_size,
+                                  Tensor<T, device> *fwd_send_buff, Tensor<T, device> *fwd_recv_buff,
+                                  Tensor<T, device> *bwd_send_buff, Tensor<T, device> *bwd_recv_buff,
+                                  Tensor<T, device> *ep_send_buffer, Tensor<T, device> *ep_recv_buffer, uint64_t ep_alltoall_size,
+                                  ProxyCommunicator *dp_communicator, ProxyCommunicator *pp_communicator,
+                                  ProxyCommunicator *ep_communicator) {
+    auto expert_parallel_exchange = [&] { // tokens to the experts and back, for every MoE layer of the stage
+        for (int k = 0; k < 2 * layers_per_stage; k++) {
+            timer_ep_comm.start();
+            ep_communicator->Alltoall(ep_send_buffer->data, (int)ep_alltoall_size, ep_recv_buffer->data, (int)ep_alltoall_size);
+            timer_ep_comm.stop();
+        }
+    };
+    const bool first = stage_id == 0, last = stage_id == num_stage - 1;
+    auto timed = [&](auto &&call) {
+        timer_pp_comm.start();
+        call();
+        timer_pp_comm.stop();
+    };
+    for (int mb = 0; mb < num_microbatches; mb++) { // forward: activations flow down the pipeline
+        if (!first) timed([&] { pp_communicator->recv(fwd_recv_buff->data, (int)pipe_msg_size, stage_id - 1); });
+        emulate_compute(fwd_rt);
+        if (!last) timed([&] { pp_communicator->send(fwd_send_buff->data, (int)pipe_msg_size, stage_id + 1); });
+        expert_parallel_exchange();
+    }
+    for (int mb = 0; mb < num_microbatches; mb++) { // backward: gradients flow back up
+        if (!last) timed([&] { pp_communicator->recv(bwd_recv_buff->data, (int)pipe_msg_size, stage_id + 1); });
+        emulate_compute(bwd_rt);
+        if (!first) timed([&] { pp_communicator->send(bwd_send_buff->data, (int)pipe_msg_size, stage_id - 1); });
+        expert_parallel_exchange();
+    }
+    timer_dp_ep_comm.start(); // non-expert gradients across the expert group
+    ep_communicator->Allreduce(grad_ptr->data, sum_grad_ptr->data, (int)non_expert_size);
+    timer_dp_ep_comm.stop();
+    timer_dp_comm.start();
+    dp_communicator->Allreduce(grad_ptr->data, sum_grad_ptr->data, (int)dp_allreduce_size);
+    timer_dp_comm.stop();
+    return 0;
+}
+
+static void print_help(const char *prog) {
+    printf("Usage: %s <model> <num_stages> <num_microbatches> <num_expert_shards> <base_path> [options]\n\n"
+           "Arguments:\n"
+           "  model              Name of the model to use (model_stats/<model>.txt, models/<family>.json)\n"
+           "  num_stages         Number of pipeline stages\n"
+           "  num_microbatches   Number of microbatches\n"
+           "  num_expert_shards  Number of expert parallel shards\n"
+           "  base_path          Base path for the repository (relative to the current directory)\n\n",
+           prog);
+    b200::print_options_help();
+}
+
+template <typename T> static int proxy_main(const b200::Cli &cli, const b200::World &w) {
+    const std::string model_name = cli.positional[0];
+    const int num_stage = atoi(cli.positional[1].c_str()), num_microbatches = atoi(cli.positional[2].c_str());
+    const int num_expert_shards = atoi(cli.positional[3].c_str());
+    if (num_stage <= 0 || num_microbatches <= 0 || num_expert_shards <= 0) {
+        fprintf(stderr, "Error: num_stages, num_microbatches and num_expert_shards must be positive\n");
+        return 1;
+    }
+    const fs::path repo = get_dnnproxy_base_path(cli.positional[4].c_str());
+    const fs::path stats_file = repo / "model_stats" / (model_name + ".txt");
+    // models/<family>.json: the stats name without its two trailing _<batch>_<dtype> fields
+    std::string family = model_name.substr(0, model_name.find_last_of('_'));
+    family = family.substr(0, family.find_last_of('_'));
+    if (!fs::exists(stats_file)) {
+        std::cerr << "Error: model stats file does not exist: " << stats_file << "\n";
+        return -1;
+    }
+    const unsigned num_layers = count_layers((repo / "models" / (family + ".json")).string());
+    std::map<std::string, uint64_t> stats = get_model_stats(stats_file.string());
+    const unsigned local_batch_size = (unsigned)stats["batchSize"];
+    const uint64_t total_model_size = stats["modelSize"];
+    const uint64_t non_expert_model_size = stats["nonExpertModelSize"];
+    const int num_experts = (int)stats["experts"];
+    if (num_experts <= 0) {
+        std::cerr << "Error: Invalid number of experts in model stats: " << num_experts << "\n";
+        return -1;
+    }
+    // per stage, then per micro-batch (integer divisions, as the reference)
+    const uint64_t fwd_rt_per_microbatch = stats["avgForwardTime"] / num_stage / (uint64_t)num_microbatches;
+    const uint64_t bwd_rt_per_microbatch = stats["avgBackwardTime"] / num_stage / (uint64_t)num_microbatches;
+    const uint64_t samples_per_microbatch = local_batch_size / num_microbatches;
+    const uint64_t sequence_length = stats["sequenceLength"], embedded_dim = stats["embeddedDim"];
+    const uint64_t pipe_msg_size = sequence_length * samples_per_microbatch * embedded_dim;
+    // every rank sends each of the E ranks tokens * top_k * dim / E elements (uniform routing, top_k = 2)
+    const int top_k = 2;
+    const uint64_t ep_alltoall_size = samples_per_microbatch * sequence_length * top_k * embedded_dim / (uint64_t)num_expert_shards;
+    const uint64_t non_expert_size = non_expert_model_size / num_stage;
+    const uint64_t expert_size = (total_model_size - non_expert_model_size) / num_stage / num_expert_shards;
+    const uint64_t dp_allreduce_size = non_expert_size + expert_size;
+    if (num_layers % num_stage != 0 || local_batch_size % num_microbatches != 0 || num_experts % num_expert_shards != 0 ||
+        w.size % (num_stage * num_expert_shards) != 0) {
+        fprintf(stderr, "Error: layers (%u) must be a multiple of the stages (%d), the batch (%u) of the microbatches (%d), the "
+                        "experts (%d) of the expert shards (%d), the world size (%d) of stages x expert shards\n", num_layers,
+                num_stage, local_batch_size, num_microbatches, num_experts, num_expert_shards, w.size);
+        return 1;
+    }
+    const int layers_per_stage = (int)num_layers / num_stage;
+    if (pipe_msg_size > 0x7fffffffull || dp_allreduce_size > 0x7fffffffull || ep_alltoall_size > 0x7fffffffull) {
+        fprintf(stderr, "Error: message of %llu elements does not fit the interface's int count (the reference would wrap)\n",
+                (unsigned long long)std::max(std::max(pipe_msg_size, dp_allreduce_size), ep_alltoall_size));
+        return 1;
+    }
+
+    const int my_device = set_local_device(w.local_rank, cli.devices.c_str());
+    b200::check(dlnb_init(w.rank, w.size, my_device, w.session.c_str()), "dlnb_init");
+    print_topology_graph();
+    {
+        char line[128];
+        snprintf(line, sizeof(line), "Rank %d using device %d\n", w.rank, my_device);
+        b200::print_all_ordered(line);
+    }
+    b200::check(dlnb_set("spin_ctas", cli.spin_ctas), "dlnb_set");
+
+    // rank = (dp_id * S + stage_id) * E + ep_id. EP group: same (dp, stage); PP group: same (dp, ep), in
+    // stage order; DP group: same (stage, ep).
+    const int S = num_stage, E = num_expert_shards, dp_size = w.size / (S * E);
+    const int ep_id = w.rank % E, stage_id = (w.rank / E) % S, dp_id = w.rank / (E * S);
+    std::vector<int> dp_group, pp_group, ep_group;
+    for (int i = 0; i < E; i++) ep_group.push_back((dp_id * S + stage_id) * E + i);
+    for (int i = 0; i < S; i++) pp_group.push_back((dp_id * S + i) * E + ep_id);
+    for (int i = 0; i < dp_size; i++) dp_group.push_back((i * S + stage_id) * E + ep_id);
+    B200Communicator *dp_communicator = new B200Communicator(dp_group, 1, ProxyDtype<T>::value);
+    B200Communicator *pp_communicator = new B200Communicator(pp_group, 1, ProxyDtype<T>::value);
+    B200Communicator *ep_communicator_ = new B200Communicator(ep_group, 1, ProxyDtype<T>::value);
+    dp_communicator->set("algo", b200::algo_from_name(cli.algo));
+    ep_communicator_->set("algo", b200::algo_from_name(cli.algo));
+    if (cli.ctas > 0) {
+        dp_communicator->set("ctas", cli.ctas);
+        pp_communicator->set("ctas", cli.ctas);
+        ep_communicator_->set("ctas", cli.ctas);
+    }
+
+    Tensor<T, device> *grad_ptr = new Tensor<T, device>(dp_allreduce_size), *sum_grad_ptr = new Tensor<T, device>(dp_allreduce_size);
+    Tensor<T, device> *fwd_send_buff = new Tensor<T, device>(pipe_msg_size), *fwd_recv_buff = new Tensor<T, device>(pipe_msg_size);
+    Tensor<T, device> *bwd_send_buff = new Tensor<T, device>(pipe_msg_size), *bwd_recv_buff = new Tensor<T, device>(pipe_msg_size);
+    Tensor<T, device> *ep_send_buffer = new Tensor<T, device>(ep_alltoall_size * num_expert_shards);
+    Tensor<T, device> *ep_recv_buffer = new Tensor<T, device>(ep_alltoall_size * num_expert_shards);
+    b200::check(dlnb_fill_pattern(ep_send_buffer->data, ep_alltoall_size * num_expert_shards, ProxyDtype<T>::value, DLNB_PAT_INT, 3, w.rank), "fill");
+    b200::check(dlnb_fill_pattern(grad_ptr->data, dp_allreduce_size, ProxyDtype<T>::value, DLNB_PAT_INT, 0, w.rank), "fill");
+    b200::check(dlnb_fill_pattern(fwd_send_buff->data, pipe_msg_size, ProxyDtype<T>::value, DLNB_PAT_INT, 1, w.rank), "fill");
+    b200::check(dlnb_fill_pattern(bwd_send_buff->data, pipe_msg_size, ProxyDtype<T>::value, DLNB_PAT_INT, 2, w.rank), "fill");
+    double spin_overhead_us = 0, spin_slope = 1;
+    b200::check(dlnb_spin_calibrate(&spin_overhead_us, &spin_slope), "spin calibration");
+    b200::host_barrier();
+
+    auto iteration = [&]() {
+        run_data_pipe_expert_parallel<T>(num_microbatches, stage_id, num_stage, layers_per_stage, pipe_msg_size,
+                                         fwd_rt_per_microbatch, bwd_rt_per_microbatch, grad_ptr, sum_grad_ptr, dp_allreduce_size,
+                                         non_expert_size, fwd_send_buff, fwd_recv_buff, bwd_send_buff, bwd_recv_buff, ep_send_buffer,
+                                         ep_recv_buffer, ep_alltoall_size, dp_communicator, pp_communicator, ep_communicator_);
+    };
+    std::vector<float> warmup_times;
+    for (int i = 0; i < cli.warmup; i++) {
+        const double t0 = b200::wtime();
+        iteration();
+        warmup_times.push_back((float)(b200::wtime() - t0));
+    }
+    int runs = cli.runs;
+    if (cli.min_exectime > 0) {
+        runs = estimate_runs(warmup_times, (uint64_t)cli.min_exectime);
+        b200::print_once("Estimated runs based on warm-up times to meet minimum execution time: " + std::to_string(runs) + "\n");
+    }
+
+    std::vector<float> device_ms;
+    timer_pp_comm.clear();
+    timer_dp_comm.clear();
+    timer_ep_comm.clear(); timer_dp_ep_comm.clear();
+#ifdef PROXY_LOOP
+    b200::install_stop_handlers();
+    const long bound = b200::loop_iters_from_env();
+    for (long it = 0; (bound < 0 || it < bound) && !b200::stop_flag(); it++) {
+        if (bound < 0 && device_ms.size() >= 4096) { timer_pp_comm.clear(); timer_dp_comm.clear(); timer_ep_comm.clear(); timer_dp_ep_comm.clear(); timer_runtime.clear(); device_ms.clear(); }
+        timer_runtime.start();
+        b200::check(dlnb_iter_begin(), "iter begin");
+        iteration();
+        float ms = 0;
+        b200::check(dlnb_iter_end(&ms), "iter end");
+        timer_runtime.stop();
+        device_ms.push_back(ms);
+    }
+    if (bound < 0) {
+        fprintf(stderr, "[rank %d] hybrid_3d_moe_loop stopped after %zu timed iterations, median %.3f ms (device)\n", w.rank,
+                device_ms.size(), b200::median(device_ms));
+        _exit(0);
+    }
+#else
+    for (int it = 0; it < runs; it++) {
+        timer_runtime.start();
+        b200::check(dlnb_iter_begin(), "iter begin");
+        iteration();
+        float ms = 0;
+        b200::check(dlnb_iter_end(&ms), "iter end");
+        timer_runtime.stop();
+        device_ms.push_back(ms);
+    }
+#endif
+
+    // middle stages time a recv and a send per micro-batch and direction: report their sum, one
+    // entry per micro-batch and direction, like the reference does (hybrid_2d.cpp:414-436)
+    std::vector<float> pp_times = timer_pp_comm.vals;
+    if (stage_id > 0 && stage_id < num_stage - 1) {
+        std::vector<float> merged;
+        for (size_t i = 0; i + 1 < pp_times.size(); i += 2) merged.push_back(pp_times[i] + pp_times[i + 1]);
+        pp_times.swap(merged);
+    }
+    // GPipe critical path of pure emulated compute: (M + S - 1) slots forward and backward (the
+    // all-to-alls per micro-batch are exposed communication by construction)
+    const uint64_t lower_bound_us = (uint64_t)(num_microbatches + num_stage - 1) * (fwd_rt_per_microbatch + bwd_rt_per_microbatch);
+    const std::vector<float> device_ms_max = b200::max_over_ranks(device_ms);
+    const float dp_ms = dp_communicator->slot_ms(-1);
+    const double wire = dp_size > 1 ? 2.0 * (dp_size - 1) / dp_size * (double)dp_allreduce_size * sizeof(T)
+                                    : 2.0 * (double)dp_allreduce_size * sizeof(T);
+    char host_name[256] = "localhost";
+    gethostname(host_name, sizeof(host_name) - 1);
+
+    b200::Section out("dp_pp_ep", "Data + Pipeline + Expert Parallelism");
+    out.global.put("model_name", model_name)
+        .put("num_stages", num_stage)
+        .put("num_microbatches", num_microbatches)
+        .put("num_expert_shards", num_expert_shards)
+        .put("num_experts", num_experts)
+        .put("sequence_length", sequence_length)
+        .put("embedded_dim", embedded_dim)
+        .put("samples_per_microbatch", samples_per_microbatch)
+        .put("local_batch_size", local_batch_size)
+        .put("global_batch_size", (unsigned)dp_size * local_batch_size)
+        .put("world_size", w.size)
+        .put("dp_size", dp_size)
+        .put("fwd_rt_per_microbatch", fwd_rt_per_microbatch)
+        .put("bwd_rt_per_microbatch", bwd_rt_per_microbatch)
+        .put("total_model_size_params", total_model_size)
+        .put("pipe_msg_size_bytes", pipe_msg_size * sizeof(T))
+        .put("ep_alltoall_size_bytes", ep_alltoall_size * sizeof(T))
+        .put("dp_allreduce_size_bytes", dp_allreduce_size * sizeof(T))
+        .put("device", device == Device::CPU ? "CPU" : "GPU")
+        .put("backend", dp_communicator->get_name())
+        .put("dtype", ProxyDtype<T>::name)
+        .put("arena", dlnb_arena_kind())
+        .put("lower_bound_us", lower_bound_us)
+        .put("device_iter_ms_max_over_ranks", device_ms_max)
+        .put("device_iter_ms_median", b200::median(device_ms_max))
+        .put("ratio_to_lower_bound", lower_bound_us ? b200::median(device_ms_max) * 1000.0 / (double)lower_bound_us : 0.0)
+        .put("dp_allreduce_last_ms", dp_ms)
+        .put("dp_allreduce_busbw_GBps", dp_ms > 0 ? wire / (dp_ms * 1e-3) / 1e9 : 0.0)
+        .put("kernel_launches", (uint64_t)dlnb_launch_count());
+    out.per_rank.put("runtimes", timer_runtime.vals)
+        .put("pp_comm_time", pp_times)
+        .put("dp_comm_time", timer_dp_comm.vals)
+        .put("ep_comm_time", timer_ep_comm.vals)
+        .put("dp_ep_comm_time", timer_dp_ep_comm.vals)
+        .put("hostname", host_name)
+        .put("stage_id", stage_id)
+        .put("ep_id", ep_id)
+        .put("dp_id", dp_id)
+        .put("device_runtimes_ms", device_ms);
+    out.emit();
+
+    dp_communicator->finalize();
+    pp_communicator->finalize();
+    ep_communicator_->finalize();
+    b200::check(dlnb_finalize(), "dlnb_finalize");
+    return 0;
+}
+
+int main(int argc, char *argv[]) {
+    const b200::Cli cli = b200::parse_cli(argc, argv);
+    if (!cli.ok || cli.help || cli.positional.size() != 5) {
+        print_help(argv[0]);
+        return 1;
+    }
+    const b200::World w = b200::world_from_env();
+    switch (b200::dtype_from_name(cli.dtype)) {
+    case DLNB_F32: return proxy_main<float>(cli, w);
+    case DLNB_F16: return proxy_main<proxy_half>(cli, w);
+    case DLNB_BF16: return proxy_main<proxy_bfloat16>(cli, w);
+    }
+    fprintf(stderr, "Error: unknown dtype '%s' (fp32 | fp16 | bf16)\n", cli.dtype.c_str());
+    return 1;
+}

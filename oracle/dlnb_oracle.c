@@ -189,6 +189,27 @@ void dlnb_oracle_hybrid3d_sizes(uint64_t fwd_us, uint64_t bwd_us, uint64_t model
     out[5] = out[2] / (uint64_t)num_tensor_shards;
 }
 
+/* hybrid_3d_moe.cpp:330-352 — DP + PP + expert parallel (E expert shards, top_k = 2 routing): out[0], out[1] =
+ * fwd / bwd us per micro-batch (time / stages / micro-batches), out[2] = pipe message elements
+ * (seq_len * samples per micro-batch * embed_dim, 64-bit), out[3] = DP allreduce elements = non-expert share
+ * + expert share, out[4] = compute critical path, out[5] = all-to-all elements PER PEER = tokens per
+ * micro-batch * top_k * embed_dim / E, out[6] = non-expert elements per stage (the expert group's allreduce),
+ * out[7] = all-to-alls per micro-batch and direction = 2 * layers / stages. */
+void dlnb_oracle_hybrid3d_moe_sizes(uint64_t fwd_us, uint64_t bwd_us, uint64_t model_size, uint64_t non_expert_size,
+                                    uint64_t batch, uint64_t seq_len, uint64_t embed_dim, uint64_t num_layers, int num_stages,
+                                    int num_microbatches, int num_expert_shards, uint64_t *out) {
+    const uint64_t S = (uint64_t)num_stages, M = (uint64_t)num_microbatches, E = (uint64_t)num_expert_shards;
+    const uint64_t samples = batch / M, top_k = 2;
+    out[0] = fwd_us / S / M;
+    out[1] = bwd_us / S / M;
+    out[2] = seq_len * samples * embed_dim;
+    out[6] = non_expert_size / S;
+    out[3] = out[6] + (model_size - non_expert_size) / S / E;
+    out[4] = (M + S - 1) * (out[0] + out[1]);
+    out[5] = samples * seq_len * top_k * embed_dim / E;
+    out[7] = 2 * (num_layers / S);
+}
+
 /* utils.hpp:145-159 — mean and population standard deviation, float arithmetic. */
 void dlnb_oracle_msg_stats(const uint64_t *sizes, int n, unsigned mult, float *avg_out, float *std_out) {
     float avg = 0.0f;

@@ -44,6 +44,7 @@ def lib():
         L.dlnb_oracle_fsdp_lower_bound_us.restype = u64
         L.dlnb_oracle_hybrid2d_sizes.argtypes = [u64, u64, u64, u64, u64, u64, i, i, C.POINTER(u64)]
         L.dlnb_oracle_hybrid3d_sizes.argtypes = [u64, u64, u64, u64, u64, u64, i, i, i, C.POINTER(u64)]
+        L.dlnb_oracle_hybrid3d_moe_sizes.argtypes = [u64, u64, u64, u64, u64, u64, u64, u64, i, i, i, C.POINTER(u64)]
         L.dlnb_oracle_msg_stats.argtypes = [C.POINTER(u64), i, C.c_uint, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.dlnb_oracle_parse_model_stats.argtypes = [C.c_char_p, C.POINTER(u64)]
         L.dlnb_oracle_pattern_value.argtypes = [i, u64, i, u64]
@@ -125,6 +126,15 @@ def hybrid3d_sizes(st, num_stages, num_microbatches, num_tensor_shards):
     lib().dlnb_oracle_hybrid3d_sizes(st["avgForwardTime"], st["avgBackwardTime"], st["modelSize"], st["batchSize"],
                                      st["sequenceLength"], st["embeddedDim"], num_stages, num_microbatches, num_tensor_shards, out)
     return dict(zip(["fwd_us", "bwd_us", "pipe_elems", "dp_elems", "lower_bound_us", "tp_elems"], list(out)))
+
+
+def hybrid3d_moe_sizes(st, num_layers, num_stages, num_microbatches, num_expert_shards):
+    out = (C.c_uint64 * 8)()
+    lib().dlnb_oracle_hybrid3d_moe_sizes(st["avgForwardTime"], st["avgBackwardTime"], st["modelSize"], st["nonExpertModelSize"],
+                                         st["batchSize"], st["sequenceLength"], st["embeddedDim"], num_layers, num_stages,
+                                         num_microbatches, num_expert_shards, out)
+    return dict(zip(["fwd_us", "bwd_us", "pipe_elems", "dp_elems", "lower_bound_us", "a2a_elems_per_peer", "non_expert_elems",
+                     "a2a_per_microbatch"], list(out)))
 
 
 def msg_stats(sizes, mult=1):

@@ -135,6 +135,22 @@ def test_hybrid_3d_cli_and_argument_checks():
     assert res.returncode == 1 and "stages x tensor shards" in res.stderr
 
 
+def test_hybrid_3d_moe_cli_and_argument_checks():
+    exe = os.path.join(ROOT, "bin", "b200", "cpp", "hybrid_parallel", "hybrid_3d_moe")
+    res = subprocess.run([exe, "-h"], capture_output=True, text=True, cwd=ROOT)
+    assert res.returncode == 1 and "num_expert_shards" in res.stdout
+    env = {**os.environ, "DLNB_WORLD": "8", "DLNB_RANK": "0"}
+    # 4 experts over 3 shards / 8 ranks over 2 x 3: refused like the reference's checks (hybrid_3d_moe.cpp:296-311)
+    res = subprocess.run([exe, "moe_tiny_8_bfloat16", "2", "4", "3", "tests/data"], capture_output=True, text=True, cwd=ROOT, env=env)
+    assert res.returncode == 1 and "expert shards" in res.stderr, res.stderr
+    # a dense table has Experts:1, which two shards do not divide
+    res = subprocess.run([exe, "gpt2_l_16_bfloat16", "2", "4", "2", "."], capture_output=True, text=True, cwd=ROOT, env=env)
+    assert res.returncode == 1 and "the experts (1) of the expert shards (2)" in res.stderr, res.stderr
+    # the one MoE table upstream ships needs more than 2^31 elements per buffer on 8 ranks: refused, not wrapped
+    res = subprocess.run([exe, "mixtral_8x7b_16_bfloat16", "2", "4", "2", "."], capture_output=True, text=True, cwd=ROOT, env=env)
+    assert res.returncode == 1 and "does not fit the interface's int count" in res.stderr, res.stderr
+
+
 def test_count_layers_reads_the_model_json(tmp_path):
     src = tmp_path / "t.cpp"
     src.write_text('#include "utils.hpp"\nint main(int c,char**v){printf("%u\\n",count_layers(v[1]));}\n')

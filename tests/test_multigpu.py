@@ -62,6 +62,27 @@ def test_proxy_binaries_on_2_gpus(prog, args, section):
     assert 1.0 <= g["ratio_to_lower_bound"] < 1.25, g["ratio_to_lower_bound"]
 
 
+def test_hybrid_3d_moe_on_2_gpus_two_expert_shards():
+    """One stage, two expert shards on the synthetic MoE table: 2 * layers all-to-alls per micro-batch and direction."""
+    if GPU_COUNT < 2:
+        pytest.skip("needs 2 GPUs")
+    from dlnetbench_b200.parser import parse_sections
+
+    res = subprocess.run([os.path.join(ROOT, "bin", "dlnb_launch"), "-n", "2",
+                          os.path.join(ROOT, "bin", "b200", "cpp", "hybrid_parallel", "hybrid_3d_moe"),
+                          "moe_tiny_8_bfloat16", "1", "2", "2", "tests/data", "-t", "fp16", "-r", "3"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    sec = parse_sections(res.stdout)["dp_pp_ep"]
+    g, ro = sec["json_data"], sec["rank_outputs"]
+    assert g["backend"] == "B200P2P" and g["num_experts"] == 4 and g["dp_size"] == 1
+    assert g["ep_alltoall_size_bytes"] == 4 * 256 * 2 * 512 // 2 * 2 and g["dp_allreduce_size_bytes"] == (8_000_000 + 16_000_000) * 2
+    assert [(ro[r]["stage_id"], ro[r]["ep_id"], ro[r]["dp_id"]) for r in range(2)] == [(0, 0, 0), (0, 1, 0)]
+    assert len(ro[0]["ep_comm_time"]) == 3 * 2 * 2 * (2 * 4) and len(ro[0]["dp_ep_comm_time"]) == 3
+    # 32 blocking all-to-alls of 1 MiB per peer against 12 ms of emulated compute
+    assert 1.0 <= g["ratio_to_lower_bound"] < 1.5, g["ratio_to_lower_bound"]
+
+
 def test_hybrid_3d_on_4_gpus_two_stages_two_shards():
     if GPU_COUNT < 4:
         pytest.skip("needs 4 GPUs")

@@ -101,7 +101,7 @@ def test_half_and_bf16_conversions_match_numpy(oracle):
 def test_sizing_rules_match_reference_outputs(oracle):
     """Bucket/shard sizes and per-unit times as the reference's own binaries printed them."""
     gold = json.load(open(os.path.join(GOLD, "ref_proxy_outputs.json")))
-    assert {g["prog"] for g in gold} == {"dp", "fsdp", "hybrid_2d", "hybrid_3d"}
+    assert {g["prog"] for g in gold} == {"dp", "fsdp", "hybrid_2d", "hybrid_3d", "hybrid_3d_moe"}
     for g in gold:
         if g["prog"].startswith("hybrid"):
             continue  # checked in test_hybrid2d_sizing_matches_reference_outputs
@@ -169,6 +169,28 @@ def test_hybrid3d_sizing_matches_reference_outputs(oracle):
         runs = g["rank_keys"]["runtimes"]
         assert g["rank_keys"]["tp_comm_time"] == runs * 4 * mbs and g["rank_keys"]["dp_comm_time"] == runs
         assert set(g["rank_keys"]) >= {"stage_id", "tp_id", "dp_id", "pp_comm_time"}
+
+
+def test_hybrid3d_moe_sizing_matches_reference_outputs(oracle):
+    """DP + PP + EP sizing against what the reference binary printed for the synthetic MoE table (tests/data)."""
+    gold = [g for g in json.load(open(os.path.join(GOLD, "ref_proxy_outputs.json"))) if g["prog"] == "hybrid_3d_moe"]
+    assert len(gold) == 2
+    for g in gold:
+        G = g["global"]
+        stages, mbs, ep = int(g["args"][1]), int(g["args"][2]), int(g["args"][3])
+        st = oracle.parse_model_stats(os.path.join(ROOT, g["args"][4], "model_stats", g["args"][0] + ".txt"))
+        layers = json.load(open(os.path.join(ROOT, g["args"][4], "models", "moe_tiny.json")))["num_decoder_blocks"]
+        z = oracle.hybrid3d_moe_sizes(st, layers, stages, mbs, ep)
+        assert G["fwd_rt_per_microbatch"] == z["fwd_us"] and G["bwd_rt_per_microbatch"] == z["bwd_us"]
+        assert G["pipe_msg_size_bytes"] == z["pipe_elems"] * 4
+        assert G["ep_alltoall_size_bytes"] == z["a2a_elems_per_peer"] * 4
+        assert G["dp_allreduce_size_bytes"] == z["dp_elems"] * 4 and G["dp_size"] == g["world"] // (stages * ep)
+        assert G["num_experts"] == st["experts"] and G["global_batch_size"] == G["dp_size"] * st["batchSize"]
+        runs = g["rank_keys"]["runtimes"]
+        assert g["rank_keys"]["ep_comm_time"] == runs * 2 * mbs * z["a2a_per_microbatch"]
+        assert g["rank_keys"]["dp_ep_comm_time"] == runs and g["rank_keys"]["dp_comm_time"] == runs
+        assert set(g["rank_keys"]) >= {"stage_id", "ep_id", "dp_id", "pp_comm_time"}
+        assert z["non_expert_elems"] <= z["dp_elems"]
 
 
 def test_baseline_sizes_and_lower_bounds(oracle):
