@@ -592,6 +592,7 @@ extern "C" int dlnb_symm_alloc(size_t bytes, void **ptr) {
 extern "C" int dlnb_symm_free(void *) { return 0; }
 
 extern "C" int dlnb_set(const char *key, long value) {
+    if (!key) return fail("dlnb_set: null key");
     if (!strcmp(key, "spin_ctas")) G.spin_ctas = std::max(1L, value);
     else if (!strcmp(key, "spin_threads")) G.spin_threads = std::min(1024L, std::max(1L, value));
     else if (!strcmp(key, "slot_timing")) G.slot_timing = value;
@@ -601,6 +602,7 @@ extern "C" int dlnb_set(const char *key, long value) {
     return 0;
 }
 extern "C" long dlnb_get(const char *key) {
+    if (!key) return -1;
     if (!strcmp(key, "spin_ctas")) return G.spin_ctas;
     if (!strcmp(key, "spin_threads")) return G.spin_threads;
     if (!strcmp(key, "slot_timing")) return G.slot_timing;
@@ -652,7 +654,10 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
         CU_TRY(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
     }
     if (const char *v = getenv("DLNB_CTAS")) c->ctas = atol(v);
-    if (const char *v = getenv("DLNB_THREADS")) c->threads = atol(v);
+    if (const char *v = getenv("DLNB_THREADS")) {
+        const long t = atol(v);
+        if (t >= 32 && t <= 512 && t % 32 == 0) c->threads = t;
+    }
     if (const char *v = getenv("DLNB_ALGO")) c->algo = atol(v);
     if (const char *v = getenv("DLNB_TWOSHOT_MIN_BYTES")) c->twoshot_min_bytes = atol(v);
     if (const char *v = getenv("DLNB_MULTIMEM_MIN_BYTES")) c->multimem_min_bytes = atol(v);
@@ -673,9 +678,13 @@ extern "C" int dlnb_comm_destroy(dlnb_comm_t c) {
 extern "C" int dlnb_comm_rank(dlnb_comm_t c) { return c ? c->me : -1; }
 extern "C" int dlnb_comm_size(dlnb_comm_t c) { return c ? c->n : -1; }
 extern "C" int dlnb_comm_set(dlnb_comm_t c, const char *key, long value) {
-    if (!c) return fail("dlnb_comm_set: null communicator");
+    if (!c || !key) return fail("dlnb_comm_set: null argument");
     if (!strcmp(key, "ctas")) c->ctas = value;
-    else if (!strcmp(key, "threads")) c->threads = value;
+    else if (!strcmp(key, "threads")) {
+        // the tile layout and the flag barrier assume whole warps and the kernels' launch bound
+        if (value < 32 || value > 512 || value % 32) return fail("dlnb_comm_set: threads must be a multiple of 32 in 32..512, got %ld", value);
+        c->threads = value;
+    }
     else if (!strcmp(key, "algo")) c->algo = value;
     else if (!strcmp(key, "twoshot_min_bytes")) c->twoshot_min_bytes = value;
     else if (!strcmp(key, "multimem_min_bytes")) c->multimem_min_bytes = value;
@@ -684,7 +693,7 @@ extern "C" int dlnb_comm_set(dlnb_comm_t c, const char *key, long value) {
     return 0;
 }
 extern "C" long dlnb_comm_get(dlnb_comm_t c, const char *key) {
-    if (!c) return -1;
+    if (!c || !key) return -1;
     if (!strcmp(key, "ctas")) return c->ctas;
     if (!strcmp(key, "threads")) return c->threads;
     if (!strcmp(key, "algo")) return c->algo;
@@ -996,6 +1005,7 @@ extern "C" int dlnb_barrier(dlnb_comm_t c) {
     NEED_INIT();
     if (G.capturing) return 0;
     if (!c) return fail("null communicator");
+    if (drain_lane1_into_lane0()) return 1; // both lanes: lane 0 finishes after whatever lane 1 has in flight
     CU_TRY(cudaStreamSynchronize(G.s_comm));
     return check_watchdog();
 }
@@ -1106,16 +1116,20 @@ extern "C" int dlnb_recv(dlnb_comm_t c, void *buf, size_t count, int source) {
 // ---------------------------------------------------------------------------
 extern "C" int dlnb_iter_begin(void) {
     NEED_INIT();
-    // the iteration starts when both streams are idle up to here
+    if (G.capturing) return fail("dlnb_iter_begin inside a graph capture (time the replay instead)");
+    // the iteration starts when all streams are idle up to here, and nothing of it starts earlier
+    if (drain_lane1_into_lane0()) return 1;
     CU_TRY(cudaEventRecord(G.ev_join, G.s_comm));
     CU_TRY(cudaStreamWaitEvent(G.s_compute, G.ev_join, 0));
     CU_TRY(cudaEventRecord(G.ev_iter0, G.s_compute));
     CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_iter0, 0));
+    CU_TRY(cudaStreamWaitEvent(G.s_comm2, G.ev_iter0, 0));
     CU_TRY(cudaStreamWaitEvent(G.s_copy, G.ev_iter0, 0));
     return 0;
 }
 extern "C" int dlnb_batch_begin(void) {
     NEED_INIT();
+    if (G.capturing) return fail("dlnb_batch_begin inside a graph capture");
     // starts the device timer ON THE COMMUNICATION STREAM, behind everything enqueued so far on
     // any stream: with a long spin enqueued first, the host can queue a whole batch of
     // collectives before the first one runs, and dlnb_iter_end() then reads pure device time.
@@ -1129,6 +1143,7 @@ extern "C" int dlnb_batch_begin(void) {
 }
 extern "C" int dlnb_iter_end(float *ms) {
     NEED_INIT();
+    if (G.capturing) return fail("dlnb_iter_end inside a graph capture (time the replay instead)");
     G.compute_dirty = true;
     G.copy_dirty = true;
     if (join_streams()) return 1;
