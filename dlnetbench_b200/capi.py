@@ -153,6 +153,12 @@ class Tensor:
         check(lib().dlnb_symm_alloc(self.size * DTYPE_SIZE[dtype], C.byref(p)))
         self.data = p.value
 
+    def free(self) -> None:
+        """dlnb_symm_free: collective like the allocation; the block may be handed out again (cleared)."""
+        if self.data:
+            check(lib().dlnb_symm_free(self.data))
+            self.data = None
+
     @property
     def nbytes(self) -> int:
         return self.size * DTYPE_SIZE[self.dtype]

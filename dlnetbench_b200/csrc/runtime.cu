@@ -19,9 +19,11 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <map>
 #include <string>
 #include <vector>
 
+#include "arena_layout.hpp"
 #include "aux_kernels.cuh"
 #include "bootstrap.hpp"
 #include "launch.hpp"
@@ -138,7 +140,8 @@ enum ArenaKind { ARENA_LOCAL = 0, ARENA_VMM = 1, ARENA_IPC = 2 };
 
 struct Chunk {
     char *local = nullptr;
-    size_t size = 0, used = 0;
+    size_t size = 0;
+    ChunkLayout layout; // which bytes of the chunk are handed out (identical on every rank)
     char *peer[MAXR] = {};                   // my mapping of world rank p's copy
     CUmemGenericAllocationHandle handle = 0; // VMM only
     std::vector<CUmemGenericAllocationHandle> imported;
@@ -182,6 +185,8 @@ struct State {
     bool capturing = false, comm_in_capture = false; // between dlnb_graph_begin and dlnb_graph_end
     // arena
     std::vector<Chunk> chunks;
+    struct Alloc { int chunk; size_t off, size; };
+    std::map<const void *, Alloc> allocs; // live dlnb_symm_alloc blocks by local address
     size_t gran = 2u << 20, min_chunk = 256u << 20, va_size = 0, va_used = 0;
     CUdeviceptr window[MAXR] = {};
     size_t bytes_in_use = 0;
@@ -358,19 +363,53 @@ static int arena_grow(size_t need) {
         std::string e = G.boot.barrier(); // peers' mappings exist before anyone uses them
         if (!e.empty()) return fail("%s", e.c_str());
     }
+    c.layout = ChunkLayout(c.size);
     G.chunks.push_back(std::move(c));
+    return 0;
+}
+
+static int arena_sync_all_ranks() {
+    CU_TRY(cudaDeviceSynchronize());
+    if (G.boot.active()) {
+        std::string e = G.boot.barrier();
+        if (!e.empty()) return fail("%s", e.c_str());
+    }
     return 0;
 }
 
 static int arena_alloc(size_t bytes, void **out) {
     const size_t need = round_up(std::max<size_t>(bytes, 1), 1024);
-    if (G.chunks.empty() || G.chunks.back().used + need > G.chunks.back().size) {
+    int ci = -1;
+    size_t off = 0;
+    bool recycled = false;
+    for (size_t i = 0; i < G.chunks.size() && ci < 0; ++i)
+        if (G.chunks[i].layout.take(need, &off, &recycled)) ci = (int)i;
+    if (ci < 0) {
         if (arena_grow(need)) return 1;
+        ci = (int)G.chunks.size() - 1;
+        if (!G.chunks[(size_t)ci].layout.take(need, &off, &recycled)) return fail("symmetric arena: a fresh chunk cannot hold %zu bytes", need);
     }
-    Chunk &c = G.chunks.back();
-    *out = c.local + c.used;
-    c.used += need;
+    Chunk &c = G.chunks[(size_t)ci];
+    if (recycled) {
+        // The block has held data. Peers may still be reading or writing the old contents through
+        // their mappings, and a peer's kernel may push into the new block as soon as that peer's
+        // dlnb_symm_alloc returns: everybody idle -> clear -> everybody cleared.
+        if (arena_sync_all_ranks()) return 1;
+        CU_TRY(cudaMemset(c.local + off, 0, need));
+        if (arena_sync_all_ranks()) return 1;
+    }
+    *out = c.local + off;
+    G.allocs[*out] = State::Alloc{ci, off, need};
     G.bytes_in_use += need;
+    return 0;
+}
+
+static int arena_free(void *p) {
+    auto it = G.allocs.find(p);
+    if (it == G.allocs.end()) return fail("dlnb_symm_free: %p is not a live dlnb_symm_alloc block", p);
+    G.chunks[(size_t)it->second.chunk].layout.give_back(it->second.off, it->second.size);
+    G.bytes_in_use -= it->second.size;
+    G.allocs.erase(it);
     return 0;
 }
 
@@ -545,6 +584,7 @@ extern "C" int dlnb_finalize(void) {
         }
     }
     G.chunks.clear();
+    G.allocs.clear();
     if (G.kind == ARENA_VMM)
         for (int r = 0; r < G.world; ++r)
             if (G.window[r]) drv.MemAddressFree(G.window[r], G.va_size);
@@ -589,7 +629,11 @@ extern "C" int dlnb_symm_alloc(size_t bytes, void **ptr) {
     if (!ptr) return fail("dlnb_symm_alloc: null out pointer");
     return arena_alloc(bytes, ptr);
 }
-extern "C" int dlnb_symm_free(void *) { return 0; }
+extern "C" int dlnb_symm_free(void *ptr) {
+    NEED_INIT();
+    if (!ptr) return 0;
+    return arena_free(ptr);
+}
 
 extern "C" int dlnb_set(const char *key, long value) {
     if (!key) return fail("dlnb_set: null key");

@@ -79,8 +79,11 @@ int dlnb_host_allgather(const void *in, size_t bytes, void *out);
  * (cpp/proxy_classes.hpp:401-405). Collective: every rank calls it in the same
  * order with the same size. Memory is zero-filled. */
 int dlnb_symm_alloc(size_t bytes, void **ptr);
-/* Replaces CCUTILS_CUDA_FREE_SAFE (proxy_classes.hpp:434). The arena is a bump
- * allocator; memory is returned at dlnb_finalize(). */
+/* Replaces CCUTILS_CUDA_FREE_SAFE (proxy_classes.hpp:434). Collective like the
+ * allocation (same order on every rank): the block goes back to the arena and a later
+ * dlnb_symm_alloc may reuse it (it is then cleared again, after all ranks went idle).
+ * The physical memory returns to the driver at dlnb_finalize(). NULL is ignored; a
+ * pointer that is not a live block is an error. */
 int dlnb_symm_free(void *ptr);
 size_t dlnb_symm_bytes_in_use(void);
 

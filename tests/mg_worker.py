@@ -134,6 +134,27 @@ def main():
         for c in comms.values():
             c.finalize()
 
+    # ---- dlnb_symm_free / reuse across ranks: recycled blocks keep their symmetric offsets and come back cleared
+    for dtype in (0, 1):
+        count = 1_000_001
+        comm = capi.B200Communicator(list(range(world)), 1, dtype)
+        a, b = capi.Tensor(count, dtype), capi.Tensor(count, dtype)
+        a.fill(1, 11, rank)
+        comm.Allreduce(a.data, b.data, count)
+        addr_a, addr_b = a.data, b.data
+        a.free()
+        b.free()
+        c, d = capi.Tensor(count, dtype), capi.Tensor(count, dtype)
+        expect((c.data, d.data) == (addr_a, addr_b), "recycled blocks land where the freed ones were")
+        zero = capi.verify_sum_pattern(d.data, count, 0, dtype, 0, 0, [0])  # PAT_ZERO: every element must be 0 again
+        expect(zero == 0, f"recycled block is cleared dtype={dtype}")
+        c.fill(1, 12, rank)
+        comm.Allreduce(c.data, d.data, count)
+        expect(capi.verify_sum_pattern(d.data, count, 0, dtype, 1, 12, list(range(world))) == 0, f"allreduce on recycled blocks dtype={dtype}")
+        comm.finalize()
+        c.free()
+        d.free()
+
     # ---- point-to-point (pipeline stages): ring exchange with Irecv/Isend, then a blocking chain
     # (needs the contiguous VMM windows; the cudaIpc diagnostic arena does not offer send/recv)
     if world > 1 and capi.lib().dlnb_arena_kind() == b"vmm":

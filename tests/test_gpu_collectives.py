@@ -180,6 +180,39 @@ def test_error_behaviour(dl):
     comm.finalize()
 
 
+def test_symm_free_recycles_cleared_blocks(dl):
+    """dlnb_symm_free gives the block back; the next allocation of that size gets the same place, zero-filled again."""
+    L = dl.lib()
+    keep = dl.Tensor(1000, 0)                       # something live below, so the freed block is not the first one
+    base = L.dlnb_symm_bytes_in_use()
+    a = dl.Tensor(300_000, 1)
+    a.fill(dl.PAT_INT, 5, 3)
+    assert a.checksum() != dl.Tensor(300_000, 1).checksum()  # a holds data, a fresh tensor is zeros
+    zero_sum = dl.Tensor(300_000, 1).checksum()
+    addr = a.data
+    in_use = L.dlnb_symm_bytes_in_use()
+    a.free()
+    assert L.dlnb_symm_bytes_in_use() < in_use
+    b = dl.Tensor(300_000, 1)
+    assert b.data == addr and b.checksum() == zero_sum        # first fit: same place, cleared
+    with pytest.raises(dl.DlnbError):
+        dl.check(L.dlnb_symm_free(b.data + 1024))             # not the start of a live block
+    b.free()
+    with pytest.raises(dl.DlnbError):
+        dl.check(L.dlnb_symm_free(addr))                      # double free
+    dl.check(L.dlnb_symm_free(None))                          # NULL is ignored
+    assert L.dlnb_symm_bytes_in_use() >= base
+    # a recycled block works as a collective buffer
+    c, d = dl.Tensor(300_000, 1), dl.Tensor(300_000, 1)
+    c.fill(dl.PAT_INT, 9, 0)
+    comm = dl.B200Communicator([0], 1, 1)
+    comm.Allreduce(c.data, d.data, 300_000)
+    assert c.checksum() == d.checksum()
+    comm.finalize()
+    for t in (c, d, keep):
+        t.free()
+
+
 def test_spin_kernel_duration(dl):
     """Chained spins last the sum of the requests (device-timed); the fixed cost of the
     begin/end event plumbing (~10-25 us per bracket) is amortised over the chain."""

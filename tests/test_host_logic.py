@@ -86,6 +86,14 @@ def test_rendezvous_allgather_and_fd_exchange(tmp_path):
         assert res.returncode == 0 and "OK" in res.stdout, res.stdout + res.stderr
 
 
+def test_arena_layout_placement_logic(tmp_path):
+    """ChunkLayout (dlnb_symm_alloc / dlnb_symm_free placement): no overlap, deterministic, coalescing, recycled flag."""
+    exe = tmp_path / "arena_layout_test"
+    subprocess.check_call(["g++", "-O1", "-std=c++17", "-Wall", "-o", str(exe), os.path.join(ROOT, "tests", "cpp", "arena_layout_test.cpp")])
+    res = subprocess.run([str(exe)], capture_output=True, text=True, timeout=60)
+    assert res.returncode == 0 and "OK" in res.stdout, res.stdout + res.stderr
+
+
 def test_launcher_sets_rank_env_and_propagates_failure():
     launch = os.path.join(ROOT, "bin", "dlnb_launch")
     res = subprocess.run([launch, "-n", "3", "sh", "-c", "echo r=$DLNB_RANK w=$DLNB_WORLD s=$DLNB_SESSION"], capture_output=True, text=True)
