@@ -37,7 +37,7 @@ int run_data_parallel(Tensor<T, device> **grad_ptrs, Tensor<T, device> **sum_gra
     emulate_compute(fwd_rt_whole_model);
     for (int i = 0; i < num_buckets; i++) {
         emulate_compute((uint64_t)bwd_rt_per_B); // usleep(float) truncates the same way
-        communicator->Iallreduce(grad_ptrs[i]->data, sum_grad_ptrs[i]->data, (int)params_per_bucket[i], i);
+        proxy_iallreduce(communicator, grad_ptrs[i]->data, sum_grad_ptrs[i]->data, params_per_bucket[i], i); // int when it fits
     }
     timer_barrier.start();
     communicator->WaitAll(num_buckets);
@@ -76,11 +76,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
     std::vector<uint64_t> params_per_bucket((size_t)num_buckets);
     for (int i = 0; i < num_buckets; i++)
         params_per_bucket[i] = total_model_size / num_buckets + ((uint64_t)i < total_model_size % num_buckets ? 1 : 0);
-    if (params_per_bucket[0] > 0x7fffffffull) {
-        fprintf(stderr, "Error: %llu elements per bucket do not fit the interface's int count; use more buckets\n",
-                (unsigned long long)params_per_bucket[0]);
-        return 1;
-    }
+    // (buckets beyond 2^31-1 elements, where the reference's int count wraps, take the backend's 64-bit entry)
 
     const int my_device = set_local_device(w.local_rank, cli.devices.c_str());
     b200::check(dlnb_init(w.rank, w.size, my_device, w.session.c_str()), "dlnb_init");

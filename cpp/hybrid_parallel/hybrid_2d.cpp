@@ -48,7 +48,7 @@ int run_data_pipe_parallel(int num_microbatches, int stage_id, int num_stage, ui
         if (!first) timed([&] { pp_communicator->send(bwd_send_buff->data, (int)pipe_msg_size, stage_id - 1); });
     }
     timer_dp_comm.start();
-    dp_communicator->Allreduce(grad_ptr->data, sum_grad_ptr->data, (int)dp_allreduce_size);
+    proxy_allreduce(dp_communicator, grad_ptr->data, sum_grad_ptr->data, dp_allreduce_size); // may exceed the interface's int
     timer_dp_comm.stop();
     return 0;
 }
@@ -95,9 +95,10 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
                         "microbatches (%d)\n", num_layers, w.size, num_stage, local_batch_size, num_microbatches);
         return 1;
     }
-    if (pipe_msg_size > 0x7fffffffull || dp_allreduce_size > 0x7fffffffull) {
-        fprintf(stderr, "Error: message of %llu elements does not fit the interface's int count\n",
-                (unsigned long long)std::max(pipe_msg_size, dp_allreduce_size));
+    // (the per-stage gradient allreduce may exceed int: it goes through proxy_allreduce's 64-bit entry)
+    if (pipe_msg_size > 0x7fffffffull) {
+        fprintf(stderr, "Error: stage-to-stage message of %llu elements does not fit the interface's int count\n",
+                (unsigned long long)pipe_msg_size);
         return 1;
     }
 

@@ -58,7 +58,7 @@ int run_data_pipe_tensor_parallel(int num_microbatches, int stage_id, int num_st
         tensor_parallel_exchange();
     }
     timer_dp_comm.start();
-    dp_communicator->Allreduce(grad_ptr->data, sum_grad_ptr->data, (int)dp_allreduce_size);
+    proxy_allreduce(dp_communicator, grad_ptr->data, sum_grad_ptr->data, dp_allreduce_size); // may exceed the interface's int
     timer_dp_comm.stop();
     return 0;
 }
@@ -109,9 +109,10 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
                 num_microbatches, w.size, num_stage * num_tensor_shards);
         return 1;
     }
-    if (pipe_msg_size > 0x7fffffffull || dp_allreduce_size > 0x7fffffffull) {
-        fprintf(stderr, "Error: message of %llu elements does not fit the interface's int count\n",
-                (unsigned long long)std::max(pipe_msg_size, dp_allreduce_size));
+    // (the per-stage gradient allreduce may exceed int: it goes through proxy_allreduce's 64-bit entry)
+    if (pipe_msg_size > 0x7fffffffull) {
+        fprintf(stderr, "Error: stage-to-stage message of %llu elements does not fit the interface's int count\n",
+                (unsigned long long)pipe_msg_size);
         return 1;
     }
 

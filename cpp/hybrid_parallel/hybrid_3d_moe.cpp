@@ -63,7 +63,7 @@ int run_data_pipe_expert_parallel(int num_microbatches, int stage_id, int num_st
     ep_communicator->Allreduce(grad_ptr->data, sum_grad_ptr->data, (int)non_expert_size);
     timer_dp_ep_comm.stop();
     timer_dp_comm.start();
-    dp_communicator->Allreduce(grad_ptr->data, sum_grad_ptr->data, (int)dp_allreduce_size);
+    proxy_allreduce(dp_communicator, grad_ptr->data, sum_grad_ptr->data, dp_allreduce_size); // may exceed the interface's int
     timer_dp_comm.stop();
     return 0;
 }
@@ -127,9 +127,11 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         return 1;
     }
     const int layers_per_stage = (int)num_layers / num_stage;
-    if (pipe_msg_size > 0x7fffffffull || dp_allreduce_size > 0x7fffffffull || ep_alltoall_size > 0x7fffffffull) {
-        fprintf(stderr, "Error: message of %llu elements does not fit the interface's int count (the reference would wrap)\n",
-                (unsigned long long)std::max(std::max(pipe_msg_size, dp_allreduce_size), ep_alltoall_size));
+    // (the gradient allreduce may exceed int — it does for mixtral_8x7b on one box — and goes through
+    // proxy_allreduce's 64-bit entry; the reference would wrap)
+    if (pipe_msg_size > 0x7fffffffull || ep_alltoall_size > 0x7fffffffull || non_expert_size > 0x7fffffffull) {
+        fprintf(stderr, "Error: message of %llu elements does not fit the interface's int count\n",
+                (unsigned long long)std::max(std::max(pipe_msg_size, non_expert_size), ep_alltoall_size));
         return 1;
     }
 

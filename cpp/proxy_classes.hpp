@@ -103,6 +103,15 @@ class B200Communicator : public ProxyCommunicator {
     }
 
     // additions
+    // 64-bit element counts (the C ABI takes size_t). The interface above counts in int, and the
+    // reference narrows its uint64_t sizes into it (dp.cpp:99, hybrid_2d.cpp:162, hybrid_3d_moe.cpp:207),
+    // which wraps beyond 2^31-1 elements — e.g. the per-stage gradients of mixtral_8x7b on one box.
+    void Allreduce64(const void *sendbuf, void *recvbuf, uint64_t count) {
+        B200_CHECK(dlnb_allreduce(comm, sendbuf, recvbuf, (size_t)count));
+    }
+    void Iallreduce64(const void *sendbuf, void *recvbuf, uint64_t count, int index) {
+        B200_CHECK(dlnb_iallreduce(comm, sendbuf, recvbuf, (size_t)count, index));
+    }
     void set(const char *key, long v) { B200_CHECK(dlnb_comm_set(comm, key, v)); }
     float slot_ms(int index) {
         float ms = 0;
@@ -132,6 +141,27 @@ class B200Communicator : public ProxyCommunicator {
     int comm_size = 1;
     int rank = 0;
 };
+
+// Allreduce of `count` elements through the interface when the count fits its int, through the
+// 64-bit entry of the B200 backend when it does not (another backend would wrap: refuse).
+inline void proxy_allreduce(ProxyCommunicator *c, const void *sendbuf, void *recvbuf, uint64_t count) {
+    if (count <= 0x7fffffffull) return c->Allreduce(sendbuf, recvbuf, (int)count);
+    B200Communicator *b = dynamic_cast<B200Communicator *>(c);
+    if (!b) {
+        fprintf(stderr, "[rank %d] allreduce of %llu elements exceeds the interface's int count\n", dlnb_rank(), (unsigned long long)count);
+        _exit(1);
+    }
+    b->Allreduce64(sendbuf, recvbuf, count);
+}
+inline void proxy_iallreduce(ProxyCommunicator *c, const void *sendbuf, void *recvbuf, uint64_t count, int index) {
+    if (count <= 0x7fffffffull) return c->Iallreduce(sendbuf, recvbuf, (int)count, index);
+    B200Communicator *b = dynamic_cast<B200Communicator *>(c);
+    if (!b) {
+        fprintf(stderr, "[rank %d] allreduce of %llu elements exceeds the interface's int count\n", dlnb_rank(), (unsigned long long)count);
+        _exit(1);
+    }
+    b->Iallreduce64(sendbuf, recvbuf, count, index);
+}
 
 enum class Device { CPU, GPU };
 

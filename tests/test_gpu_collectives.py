@@ -180,6 +180,35 @@ def test_error_behaviour(dl):
     comm.finalize()
 
 
+def test_counts_beyond_int32(dl):
+    """More than 2^31-1 elements per message (where the reference's `int count` wraps): the C ABI counts in size_t.
+    World 1 (copy path) and two virtual ranks (fused two-shot), fp16, checked on the device against the closed form
+    of the integer pattern (exact in any order)."""
+    count = (1 << 31) + 4097 + 3                     # odd tail: head/tail element paths beyond 4 GiB offsets too
+    a, b = dl.Tensor(count, 1), dl.Tensor(count, 1)
+    a.fill(dl.PAT_INT, 21, 0)
+    comm = dl.B200Communicator([0], 1, 1)
+    comm.Allreduce(a.data, b.data, count)
+    assert dl.verify_sum_pattern(b.data, count, 0, 1, dl.PAT_INT, 21, [0]) == 0
+    assert a.checksum() == b.checksum()
+    comm.finalize()
+    # two virtual ranks: r0 = a (pattern of rank 0), r1 = c (pattern of rank 1); results into b and d
+    c, d = dl.Tensor(count, 1), dl.Tensor(count, 1)
+    c.fill(dl.PAT_INT, 21, 1)
+    dl.emu_allreduce([a.data, c.data], [b.data, d.data], count, 1, algo=dl.ALGO_TWOSHOT, ctas=64)
+    assert dl.verify_sum_pattern(b.data, count, 0, 1, dl.PAT_INT, 21, [0, 1]) == 0
+    assert b.checksum() == d.checksum()
+    # the last elements, on the host, against plain arithmetic
+    tail = 8
+    got = np.empty(tail, np.float16)
+    dl.check(dl.lib().dlnb_memcpy_d2h(got.ctypes.data, b.offset(count - tail), tail * 2))
+    idx = np.arange(count - tail, count, dtype=np.uint64)
+    want = sum((((idx * np.uint64(2654435761) + np.uint64(r * 40503)) % np.uint64(17)).astype(np.int64) - 8) for r in (0, 1))
+    assert np.array_equal(got.astype(np.int64), want)
+    for t in (a, b, c, d):
+        t.free()
+
+
 def test_symm_free_recycles_cleared_blocks(dl):
     """dlnb_symm_free gives the block back; the next allocation of that size gets the same place, zero-filled again."""
     L = dl.lib()

@@ -154,8 +154,13 @@ def test_hybrid_3d_moe_cli_and_argument_checks():
     # a dense table has Experts:1, which two shards do not divide
     res = subprocess.run([exe, "gpt2_l_16_bfloat16", "2", "4", "2", "."], capture_output=True, text=True, cwd=ROOT, env=env)
     assert res.returncode == 1 and "the experts (1) of the expert shards (2)" in res.stderr, res.stderr
-    # the one MoE table upstream ships needs more than 2^31 elements per buffer on 8 ranks: refused, not wrapped
+    # the one MoE table upstream ships: 12.1e9 gradient elements per rank at this layout. The reference's int count
+    # would wrap; here the sizing passes (64-bit allreduce entry) and the run stops only because this box has no GPU
     res = subprocess.run([exe, "mixtral_8x7b_16_bfloat16", "2", "4", "2", "."], capture_output=True, text=True, cwd=ROOT, env=env)
+    if GPU_COUNT == 0:
+        assert res.returncode != 0 and "dlnb_init" in res.stderr and "int count" not in res.stderr, res.stderr
+    # a stage-to-stage message beyond int is still refused (it goes through send / recv's int)
+    res = subprocess.run([exe, "mixtral_8x7b_128_bfloat16", "2", "1", "2", "."], capture_output=True, text=True, cwd=ROOT, env=env)
     assert res.returncode == 1 and "does not fit the interface's int count" in res.stderr, res.stderr
 
 
