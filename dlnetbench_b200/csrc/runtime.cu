@@ -187,7 +187,7 @@ struct State {
     std::vector<Chunk> chunks;
     struct Alloc { int chunk; size_t off, size; };
     std::map<const void *, Alloc> allocs; // live dlnb_symm_alloc blocks by local address
-    size_t gran = 2u << 20, min_chunk = 256u << 20, va_size = 0, va_used = 0;
+    size_t gran = 2u << 20, min_chunk = (size_t)1 << 30 /* a 134 MB bucket wastes 9 % of a 1 GiB chunk, 48 % of a 256 MiB one */, va_size = 0, va_used = 0;
     CUdeviceptr window[MAXR] = {};
     size_t bytes_in_use = 0;
     // NVSwitch multicast view of the arena (in-switch reduction for large allreduces)
