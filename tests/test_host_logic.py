@@ -199,6 +199,45 @@ def test_reference_proxies_run_multirank_on_cpu_and_parse():
     assert len(sec["rank_outputs"][0]["barrier"]) == 1
 
 
+def test_metric_tables_from_sections():
+    """The frames the reference's plots read (plots/parser.py:19-196), built from a section alone. The per-unit rows
+    follow the order in which run_fsdp records its timers (fsdp.cpp:84-141)."""
+    from dlnetbench_b200.parser import dp_metrics_df, fsdp_metrics_df, parse_sections, summarize
+
+    text = "\n".join([
+        '#CCUTILS_SECTION_BEGIN dp "Data Parallelism"',
+        '#CCUTILS_GLOBAL_JSON dp {"model_name":"m","num_buckets":3,"local_batch_size":16,"world_size":2,"fwd_rt_whole_model":100,'
+        '"bwd_rt_per_bucket":10.0,"msg_size_avg_bytes":4096.0,"msg_size_std_bytes":0.0,"backend":"B200P2P","lower_bound_us":130,'
+        '"ratio_to_lower_bound":1.5}',
+        '#CCUTILS_RANK_JSON dp 0 {"runtimes":[0.2,0.1],"barrier_time":[0.05,0.01],"hostname":"h","device_runtimes_ms":[190.0,95.0]}',
+        '#CCUTILS_RANK_JSON dp 1 {"runtimes":[0.1,0.3],"barrier_time":[0.02,0.04],"hostname":"h","device_runtimes_ms":[100.0,290.0]}',
+        '#CCUTILS_SECTION_END dp',
+        '#CCUTILS_SECTION_BEGIN fsdp "Fully Sharded Data Parallelism"',
+        '#CCUTILS_GLOBAL_JSON fsdp {"model_name":"m","world_size":2,"num_units":3,"sharding_factor":2,"num_replicas":1,'
+        '"local_batch_size":8,"backend":"MPI"}',
+        # 2 runs, 3 units: 2 forward waits, 2 backward waits and 3 reduce-scatters per run, in recording order
+        '#CCUTILS_RANK_JSON fsdp 0 {"runtime":[1.0,2.0],"allgather":[0.1,0.2],"allgather_wait_fwd":[11,12,21,22],'
+        '"allgather_wait_bwd":[13,14,23,24],"reduce_scatter":[15,16,17,25,26,27],"barrier":[],"hostname":"h","rank":0}',
+        '#CCUTILS_SECTION_END fsdp'])
+    secs = parse_sections(text)
+    df = dp_metrics_df(secs["dp"])
+    assert len(df) == 4 and list(df[df["rank"] == 1]["runtime"]) == [0.1, 0.3]
+    assert {"network", "world_size", "model_name", "num_buckets", "fwd_rt_whole_model", "bwd_rt_per_bucket", "msg_size_avg_bytes",
+            "rank", "runtime", "barrier_time", "energy_consumed"} <= set(df.columns)
+    assert dp_metrics_df(secs["dp"], job_vars={"num_buckets": 99})["num_buckets"].iloc[0] == 99
+    s = summarize("dp", secs["dp"])
+    assert s["host_iter_ms_median"] == pytest.approx(250.0) and s["device_iter_ms_median"] == pytest.approx(240.0)  # max over ranks, median over runs
+    assert s["exposed_comm_tail_ms_median"] == pytest.approx(45.0) and s["ratio_to_lower_bound"] == 1.5
+    rt, comm = fsdp_metrics_df(secs["fsdp"])
+    assert len(rt) == 2 and list(rt["allgather"]) == [0.1, 0.2] and len(comm) == 6
+    run1 = comm[comm["run"] == 1].set_index("unit_idx")
+    # forward wait k is for unit k+1; backward wait k for unit U-2-k; reduce-scatter k for unit U-1-k
+    assert list(run1["allgather_wait_fwd"]) == [0, 21, 22]
+    assert list(run1["allgather_wait_bwd"]) == [24, 23, 0]
+    assert list(run1["reduce_scatter"]) == [27, 26, 25]
+    assert summarize("fsdp", secs["fsdp"])["host_iter_ms_median"] == pytest.approx(1500.0)
+
+
 @pytest.mark.skipif(not os.path.exists(os.path.join(REF, "dp")), reason="oracle/_ref not built")
 def test_bench_reference_arm_two_ranks_on_cpu():
     res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0",
