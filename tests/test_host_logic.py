@@ -44,6 +44,21 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert exported == set(names), exported ^ set(names)
 
 
+def test_header_is_plain_c_and_links_from_c(tmp_path):
+    """The boundary is a C ABI: the header compiles as C99 (no C++ or torch types) and a C program links against it."""
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
+                           os.path.join(ROOT, "include", "dlnb.h")])
+    src = tmp_path / "c_client.c"
+    src.write_text('#include <dlnb.h>\n#include <stdio.h>\n'
+                   'int main(void) { printf("%s world=%d\\n", dlnb_version(), dlnb_world());\n'
+                   '  void *p = 0; return dlnb_symm_alloc(16, &p) != 0 ? 0 : 1; /* must fail: no dlnb_init */ }\n')
+    exe = tmp_path / "c_client"
+    subprocess.check_call(["gcc", "-std=c99", "-I" + os.path.join(ROOT, "include"), "-o", str(exe), str(src),
+                           "-L" + os.path.join(ROOT, "dlnetbench_b200"), "-ldlnb", "-Wl,-rpath," + os.path.join(ROOT, "dlnetbench_b200")])
+    res = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert res.returncode == 0 and "dlnb" in res.stdout and "world=1" in res.stdout, res.stdout + res.stderr
+
+
 def test_header_cites_the_reference_for_every_replaced_call():
     text = open(os.path.join(ROOT, "include", "dlnb.h")).read()
     for needle in ("proxy_classes.hpp:32", "proxy_classes.hpp:34-35", "proxy_classes.hpp:38", "proxy_classes.hpp:41-43",
