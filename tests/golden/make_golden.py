@@ -27,12 +27,17 @@ def run_collective(op, world, count, kind, seed):
         return [np.fromfile(f"{prefix}.r{r}.bin", dtype=np.float32) for r in range(world)]
 
 
+# SURVEY 8c edge counts: 1, 7, 8, 15, 4095, 4097 and n*16 +- 1 for the group sizes in use
+COUNTS_SUM = (1, 7, 8, 15, 17, 31, 33, 127, 129, 4095, 4097)
+COUNTS_BLOCK = (1, 7, 8, 15, 17, 33, 127, 513, 1025)       # per-rank block of the gather / scatter / all-to-all ops
+
+
 def collectives():
     cases = {}
     for world in (1, 2, 3, 4, 8):
         for op in ("iallreduce", "allreduce", "iallgather", "reduce_scatter", "alltoall"):
             for kind in (1, 2):
-                for count in ((1, 7, 513) if op == "alltoall" else (1, 7, 4097)):
+                for count in COUNTS_BLOCK if op in ("alltoall", "reduce_scatter", "iallgather") else COUNTS_SUM:
                     outs = run_collective(op, world, count, kind, 1234)
                     key = f"{op}_w{world}_k{kind}_c{count}"
                     if op in ("iallreduce", "allreduce", "iallgather"):

@@ -22,7 +22,7 @@ def gold():
 def test_golden_file_covers_every_collective(gold):
     ops = {k.split("_w")[0] for k in gold.files}
     assert ops == {"iallreduce", "allreduce", "iallgather", "reduce_scatter", "alltoall"}
-    assert len(gold.files) == 5 * 5 * 2 * 3
+    assert len(gold.files) == 5 * 2 * (2 * 11 + 3 * 9)  # worlds x patterns x (sum ops x counts + block ops x counts)
 
 
 def _case(key):
