@@ -5,6 +5,7 @@
 //   allreduce one-shot / fused two-shot / in-switch (multimem)  <- MPI_Iallreduce / ncclAllReduce (SUM)
 //   allgather (push)                                            <- MPI_(I)allgather / ncclAllGather
 //   reduce-scatter (pull)                                       <- MPI_Reduce_scatter_block / ncclReduceScatter
+//   all-to-all (push)                                           <- MPI_Alltoall / grouped ncclSend + ncclRecv
 // (spin kernel, send/recv and the test helpers are in aux_kernels.cuh)
 //
 // All of them address the peers' buffers directly (VMM-mapped peer HBM over
