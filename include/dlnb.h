@@ -92,7 +92,10 @@ size_t dlnb_symm_bytes_in_use(void);
  * MPI_FLOAT, num_requests)` and MPI_Comm_split / ncclCommSplit
  * (proxy_classes.hpp:55-64,138-147; fsdp.cpp:258-283). `ranks` lists the world
  * ranks of the group in group order; must contain the caller. Collective over the
- * WORLD (every world rank creates its communicators in the same order). */
+ * WORLD (every world rank creates its communicators in the same order). A process
+ * may create at most 64 communicators between dlnb_init and dlnb_finalize: each owns
+ * a set of flag rows whose generations live on, so a destroyed communicator's set is
+ * not handed out again (the proxies create one to three). */
 int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int dtype, dlnb_comm_t *out);
 int dlnb_comm_destroy(dlnb_comm_t c);
 int dlnb_comm_rank(dlnb_comm_t c);

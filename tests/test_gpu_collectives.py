@@ -115,6 +115,7 @@ def test_cuda_path_reproduces_the_reference_golden_vectors(dl, oracle):
     sizes = {"allreduce": (1, 2, 3, 4, 8), "iallreduce": (1, 2, 3, 4, 8), "iallgather": (2, 4, 8), "reduce_scatter": (2, 4, 8),
              "alltoall": (2, 3, 8)}
     checked = 0
+    comm1 = dl.B200Communicator([0], num_slots=1, dtype=0)  # one for all world-1 cases (a process may create 64 in total)
     for key in gold.files:
         op, w, k, c = key.rsplit("_", 3)
         n, kind, count = int(w[1:]), int(k[1:]), int(c[1:])
@@ -127,9 +128,7 @@ def test_cuda_path_reproduces_the_reference_golden_vectors(dl, oracle):
         if op in ("allreduce", "iallreduce"):
             recv = [dl.Tensor(count, 0) for _ in range(n)]
             if n == 1:
-                comm = dl.B200Communicator([0], num_slots=1, dtype=0)
-                comm.Allreduce(send[0].data, recv[0].data, count)
-                comm.finalize()
+                comm1.Allreduce(send[0].data, recv[0].data, count)
             else:
                 dl.emu_allreduce([t.data for t in send], [t.data for t in recv], count, 0, algo=1 + checked % 2, ctas=4)
             got = [t.download(np.float32) for t in recv]
@@ -150,6 +149,7 @@ def test_cuda_path_reproduces_the_reference_golden_vectors(dl, oracle):
         checked += 1
         for t in send + recv:
             t.free()
+    comm1.finalize()
     assert checked >= 300
 
 
