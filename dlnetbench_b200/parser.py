@@ -119,6 +119,12 @@ def summarize(section_id: str, section: dict) -> dict:
     for k in ("lower_bound_us", "ratio_to_lower_bound", "allreduce_busbw_GBps_avg", "reduce_scatter_busbw_GBps"):
         if k in g:
             out[k] = g[k]
+    # hybrid proxies: blocking communication per category (pp / dp / tp / ep), seconds per run summed, slowest rank
+    runs = out["runs"]
+    for k in sorted({k for r in ranks.values() for k in r if k.endswith("_comm_time")}):
+        tot = [sum(r[k]) / runs for r in ranks.values() if isinstance(r.get(k), list) and r[k] and runs]
+        if tot:
+            out[k.replace("_time", "") + "_ms_per_iter_max_rank"] = max(tot) * 1e3
     tail_key = "barrier_time" if rt_key == "runtimes" and any("barrier_time" in r for r in ranks.values()) else "barrier"
     tails = [r[tail_key] for r in ranks.values() if r.get(tail_key)]
     if tails and "host_iter_ms_median" in out and out["host_iter_ms_median"] > 0:
