@@ -231,3 +231,39 @@ def test_checksum_detects_permutation(oracle):
     y[[3, 4]] = y[[4, 3]]
     assert oracle.checksum(x) != oracle.checksum(y)
     assert oracle.checksum(x) == oracle.checksum(x.copy())
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_collectives")),
+                    reason="oracle/_ref not built (needs /root/reference at build time)")
+def test_restatement_against_the_reference_live_on_random_shapes(oracle, tmp_path):
+    """Beyond the committed vectors: the reference's MPICommunicator (oracle/_ref/ref_collectives, built from the reference's
+    own proxy_classes.hpp) run HERE on shapes drawn at test time — group sizes 1..8, counts up to 200k incl. a seed-dependent
+    odd one — against the C restatement, bit for bit. Uses only oracle/_ref; nothing reads /root/reference."""
+    import subprocess
+
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    rng = np.random.default_rng(20261107)
+    ops = ["allreduce", "iallreduce", "allgather", "iallgather", "reduce_scatter", "alltoall"]
+    for case in range(18):
+        op = ops[case % len(ops)]
+        world = int(rng.integers(1, 9))
+        count = int(rng.choice([1, 3, 1000, 4099, 65537, int(rng.integers(2, 200_000))]))
+        if op in ("reduce_scatter", "alltoall", "allgather", "iallgather"):
+            count = min(count, 30_000)
+        kind, seed = int(rng.integers(1, 3)), int(rng.integers(0, 2**31))
+        prefix = str(tmp_path / f"c{case}")
+        subprocess.check_call([os.path.join(ref, "dlnb_mpirun"), "-n", str(world), os.path.join(ref, "ref_collectives"),
+                               op, str(count), str(kind), str(seed), prefix], timeout=120)
+        outs = [np.fromfile(f"{prefix}.r{r}.bin", dtype=np.float32) for r in range(world)]
+        per_rank = count if op in ("allreduce", "iallreduce", "allgather", "iallgather") else count * world
+        xs = [oracle.fill_pattern(per_rank, 0, kind, seed, r) for r in range(world)]
+        for r in range(world):
+            if op in ("allreduce", "iallreduce"):
+                want = oracle.allreduce(xs, 0)
+            elif op in ("allgather", "iallgather"):
+                want = oracle.allgather(xs, 0)
+            elif op == "reduce_scatter":
+                want = oracle.reduce_scatter_block(xs, r, count, 0)
+            else:
+                want = oracle.alltoall(xs, r, count, 0)
+            assert np.array_equal(outs[r].view(np.uint32), want.view(np.uint32)), (op, world, count, kind, seed, r)
