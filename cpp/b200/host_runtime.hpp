@@ -165,8 +165,8 @@ struct Section {
 //      additive: -t <fp32|fp16|bf16>, -a <auto|oneshot|twoshot|multimem>, -c <ctas>, -s <spin ctas>, -g ---
 struct Cli {
     std::vector<std::string> positional;
-    int warmup = 3, runs = 5, min_exectime = 0, ctas = 0, spin_ctas = 1;
-    std::string devices, dtype = "fp16", algo = "auto";
+    int warmup = 3, runs = 5, min_exectime = 0, ctas = 0, spin_ctas = -1 /* library default: one per SM */, spin_threads = 0;
+    std::string devices, dtype = "fp16", algo = "auto", spin_mode;
     bool help = false, ok = true, graph = false;
 };
 inline Cli parse_cli(int argc, char **argv) {
@@ -185,6 +185,8 @@ inline Cli parse_cli(int argc, char **argv) {
         else if (a == "-a") value(c.algo);
         else if (a == "-c") ivalue(c.ctas);
         else if (a == "-s") ivalue(c.spin_ctas);
+        else if (a == "-S") value(c.spin_mode);
+        else if (a == "-T") ivalue(c.spin_threads);
         else if (a.size() > 1 && a[0] == '-' && !isdigit((unsigned char)a[1])) c.ok = false;
         else c.positional.push_back(a);
     }
@@ -199,7 +201,9 @@ inline void print_options_help() {
            "  -t <dtype>         fp32 | fp16 | bf16 (default: fp16)          [b200 addition]\n"
            "  -a <algo>          auto | oneshot | twoshot | multimem allreduce (default: auto)  [b200 addition]\n"
            "  -c <ctas>          CTAs per collective kernel, 0 = auto        [b200 addition]\n"
-           "  -s <spin_ctas>     CTAs of the compute-emulation kernel (default: 1)  [b200 addition]\n"
+           "  -s <spin_ctas>     CTAs of the compute-emulation kernel (default: one per SM)  [b200 addition]\n"
+           "  -T <spin_threads>  Threads per CTA of the compute-emulation kernel (default: 256)  [b200 addition]\n"
+           "  -S <spin_mode>     What the emulated compute does: sleep | fma | hbm (default: fma)  [b200 addition]\n"
            "  -g                 Capture one iteration as a CUDA graph and replay it  [b200 addition]\n"
            "  -h                 Show help\n");
 }
@@ -217,6 +221,20 @@ inline int algo_from_name(const std::string &s) {
     return -1;
 }
 inline size_t dtype_bytes(int dt) { return dt == DLNB_F32 ? 4 : 2; }
+// footprint of the emulated compute from the command line (-s / -T / -S); call after dlnb_init
+inline void apply_spin_cli(const Cli &c) {
+    if (c.spin_ctas >= 0) check(dlnb_set("spin_ctas", c.spin_ctas), "dlnb_set spin_ctas");
+    if (c.spin_threads > 0) check(dlnb_set("spin_threads", c.spin_threads), "dlnb_set spin_threads");
+    if (!c.spin_mode.empty()) {
+        const long m = c.spin_mode == "sleep" ? 0 : c.spin_mode == "fma" ? 1 : c.spin_mode == "hbm" ? 2 : -1;
+        if (m < 0) die("unknown spin mode '" + c.spin_mode + "' (sleep | fma | hbm)");
+        check(dlnb_set("spin_mode", m), "dlnb_set spin_mode");
+    }
+}
+inline const char *spin_mode_name() {
+    const long m = dlnb_get("spin_mode");
+    return m == 0 ? "sleep" : m == 1 ? "fma" : "hbm";
+}
 
 // ---- *_loop binaries: run forever and print nothing (dp.cpp:251-255), unless
 //      DLNB_LOOP_ITERS bounds the loop or SIGTERM/SIGINT asks for a summary ---------------------------

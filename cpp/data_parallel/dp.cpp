@@ -86,7 +86,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         snprintf(line, sizeof(line), "Rank %d using device %d\n", w.rank, my_device);
         b200::print_all_ordered(line);
     }
-    b200::check(dlnb_set("spin_ctas", cli.spin_ctas), "dlnb_set");
+    b200::apply_spin_cli(cli);
 
     std::vector<int> everyone((size_t)w.size);
     for (int r = 0; r < w.size; r++) everyone[r] = r;
@@ -208,7 +208,10 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         .put("allreduce_slowest_ms", slowest_ms)
         .put("spin_overhead_us", spin_overhead_us)
         .put("spin_slope", spin_slope)
-        .put("spin_ctas", cli.spin_ctas)
+        .put("spin_ctas", (long)dlnb_get("spin_ctas"))
+        .put("spin_threads", (long)dlnb_get("spin_threads"))
+        .put("spin_mode", b200::spin_mode_name())
+        .put("spin_coresident", (long)dlnb_get("spin_coresident"))
         .put("cuda_graph", cli.graph)
         .put("kernel_launches", (uint64_t)dlnb_launch_count());
     dp.per_rank.put("runtimes", timer_runtime.vals)

@@ -144,7 +144,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         snprintf(line, sizeof(line), "Rank %d using device %d\n", w.rank, my_device);
         b200::print_all_ordered(line);
     }
-    b200::check(dlnb_set("spin_ctas", cli.spin_ctas), "dlnb_set");
+    b200::apply_spin_cli(cli);
 
     // unit group: the F consecutive ranks sharing rank / F; replica group: ranks with equal rank % F
     const unsigned num_replicas = (unsigned)w.size / sharding_factor;
@@ -272,8 +272,16 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         .put("reduce_scatter_busbw_GBps", rs_bus)
         .put("spin_overhead_us", spin_overhead_us)
         .put("spin_slope", spin_slope)
-        .put("spin_ctas", cli.spin_ctas)
+        .put("spin_ctas", (long)dlnb_get("spin_ctas"))
+        .put("spin_threads", (long)dlnb_get("spin_threads"))
+        .put("spin_mode", b200::spin_mode_name())
+        .put("spin_coresident", (long)dlnb_get("spin_coresident"))
         .put("cuda_graph", cli.graph)
+        // allgather_wait_* time Wait() from the moment the host reaches it. The reference's host sleeps through
+        // the compute first (usleep), so its timers hold only the wait that is LEFT; here compute is asynchronous
+        // and the timers also contain the overlapped part, unless DLNB_BLOCKING_COMPUTE=1 makes the host wait
+        // for each spin like usleep does.
+        .put("wait_timers_include_overlap", !blocking_compute && !cli.graph)
         .put("kernel_launches", (uint64_t)dlnb_launch_count());
     fsdp.emit();
 

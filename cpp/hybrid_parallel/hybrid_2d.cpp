@@ -110,7 +110,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         snprintf(line, sizeof(line), "Rank %d using device %d\n", w.rank, my_device);
         b200::print_all_ordered(line);
     }
-    b200::check(dlnb_set("spin_ctas", cli.spin_ctas), "dlnb_set");
+    b200::apply_spin_cli(cli);
 
     // DP group: the ranks with my stage (rank % S); PP group: my pipeline (rank / S), in stage order
     const int dp_size = w.size / num_stage, stage_id = w.rank % num_stage;

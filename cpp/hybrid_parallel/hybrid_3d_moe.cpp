@@ -143,7 +143,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         snprintf(line, sizeof(line), "Rank %d using device %d\n", w.rank, my_device);
         b200::print_all_ordered(line);
     }
-    b200::check(dlnb_set("spin_ctas", cli.spin_ctas), "dlnb_set");
+    b200::apply_spin_cli(cli);
 
     // rank = (dp_id * S + stage_id) * E + ep_id. EP group: same (dp, stage); PP group: same (dp, ep), in
     // stage order; DP group: same (stage, ep).

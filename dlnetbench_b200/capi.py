@@ -109,12 +109,14 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_host_free": (i, [vp]),
         "dlnb_fill_pattern": (i, [vp, sz, i, i, u64, i]),
         "dlnb_verify_sum_pattern": (i, [vp, sz, sz, i, i, u64, C.POINTER(i), i, C.POINTER(u64)]),
+        "dlnb_verify_sum_pattern_tol": (i, [vp, sz, sz, i, i, u64, C.POINTER(i), i, C.c_double, C.POINTER(u64), C.POINTER(C.c_double)]),
         "dlnb_checksum": (i, [vp, sz, C.POINTER(u64)]),
         "dlnb_flush_l2": (i, []),
         "dlnb_emu_allreduce": (i, [i, pvp, pvp, sz, i, i, i]),
         "dlnb_emu_allgather": (i, [i, pvp, pvp, sz, i, i]),
         "dlnb_emu_reduce_scatter": (i, [i, pvp, pvp, sz, i, i]),
         "dlnb_emu_allreduce_noalloc": (i, [i, pvp, pvp, sz, i, i, i]),
+        "dlnb_emu_sendrecv": (i, [vp, vp, sz, i, i]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -330,6 +332,14 @@ def verify_sum_pattern(ptr: int, count: int, elem_offset: int, dtype: int, kind:
     return out.value
 
 
+def verify_sum_pattern_tol(ptr: int, count: int, elem_offset: int, dtype: int, kind: int, seed: int, ranks, rel_tol: float):
+    """(mismatches, worst |got-ref| / sum|x|) against the rank-order fp32 sum, tolerance rel_tol * sum|x| + half an ulp."""
+    arr = (C.c_int * len(ranks))(*ranks)
+    out, worst = C.c_uint64(), C.c_double()
+    check(lib().dlnb_verify_sum_pattern_tol(ptr, count, elem_offset, dtype, kind, seed, arr, len(ranks), rel_tol, C.byref(out), C.byref(worst)))
+    return out.value, worst.value
+
+
 def _ptr_array(ptrs):
     return (C.c_void_p * len(ptrs))(*ptrs)
 
@@ -341,6 +351,18 @@ def emu_allreduce(send_ptrs, recv_ptrs, count, dtype, algo=ALGO_AUTO, ctas=0):
 def emu_allreduce_noalloc(send_ptrs, recv_ptrs, count, dtype, algo=ALGO_AUTO, ctas=0):
     """dlnb_emu_allreduce_noalloc: same result as emu_allreduce, scratch from the library image (<= 64 CTAs)."""
     check(lib().dlnb_emu_allreduce_noalloc(len(send_ptrs), _ptr_array(send_ptrs), _ptr_array(recv_ptrs), count, dtype, algo, ctas))
+
+
+def emu_sendrecv(send_ptr, recv_ptr, count, dtype, ctas=0):
+    """dlnb_emu_sendrecv: the Irecv / Isend / Wait kernels against one loop-back mailbox on one GPU."""
+    check(lib().dlnb_emu_sendrecv(send_ptr, recv_ptr, count, dtype, ctas))
+
+
+def get_option(key: str) -> int:
+    return lib().dlnb_get(key.encode())
+
+
+SPIN_SLEEP, SPIN_FMA, SPIN_HBM = 0, 1, 2
 
 
 def emu_allgather(send_ptrs, recv_ptrs, sendcount, dtype, ctas=0):

@@ -45,6 +45,7 @@ struct RankView {
     CommCtl *ctl;              // my control block
     uint32_t *host_error;      // mapped pinned word, set by the watchdog (may be null)
     unsigned long long timeout_ns;
+    int strict;                // 1: every barrier uses release/acquire flag traffic (see cta_barrier)
 };
 
 struct EmuViews {
@@ -107,16 +108,19 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
 template <typename T> struct Elem;
 template <> struct Elem<float> {
     static constexpr int PER_VEC = 4;
+    static constexpr float HALF_ULP = 5.9604645e-8f; // 2^-24: one rounding to T, relative
     static __device__ __forceinline__ float to_f(float x) { return x; }
     static __device__ __forceinline__ float from_f(float x) { return x; }
 };
 template <> struct Elem<__half> {
     static constexpr int PER_VEC = 8;
+    static constexpr float HALF_ULP = 4.8828125e-4f; // 2^-11
     static __device__ __forceinline__ float to_f(__half x) { return __half2float(x); }
     static __device__ __forceinline__ __half from_f(float x) { return __float2half_rn(x); }
 };
 template <> struct Elem<__nv_bfloat16> {
     static constexpr int PER_VEC = 8;
+    static constexpr float HALF_ULP = 3.90625e-3f; // 2^-8
     static __device__ __forceinline__ float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
     static __device__ __forceinline__ __nv_bfloat16 from_f(float x) { return __float2bfloat16_rn(x); }
 };
@@ -213,11 +217,12 @@ __device__ __forceinline__ void cta_barrier(const RankView &v, uint32_t gen, int
         const int p = threadIdx.x;
         uint32_t *theirs = v.flags[p] + (size_t)cta * FLAG_ROW + v.rank;
         const uint32_t *mine = v.flags[v.rank] + (size_t)cta * FLAG_ROW + p;
-        if (PUBLISH) st_release_sys(theirs, gen);
+        const bool fenced = PUBLISH || v.strict;
+        if (fenced) st_release_sys(theirs, gen);
         else st_relaxed_sys(theirs, gen);
         unsigned long long t0 = 0;
         unsigned polls = 0;
-        while ((int32_t)((PUBLISH ? ld_acquire_sys(mine) : ld_relaxed_sys(mine)) - gen) < 0) {
+        while ((int32_t)((fenced ? ld_acquire_sys(mine) : ld_relaxed_sys(mine)) - gen) < 0) {
             if ((++polls & 0x3ff) == 0) {
                 unsigned long long now = globaltimer_ns();
                 if (t0 == 0) t0 = now;
@@ -306,12 +311,16 @@ __device__ __forceinline__ void reduce_store_elem(const T *const *src, int nsrc,
 }
 
 template <int NR> struct Unroll {
-    // U*NR independent 128-bit loads in flight per thread, at most 16 (64 data registers)
-    static constexpr int U = NR == 1 ? 4 : NR == 2 ? 8 : NR <= 4 ? 4 : 2;
+    // U*NR independent 128-bit loads in flight per thread. The multi-rank kernels are held to 96
+    // registers (see coll_kernel) so that a compute CTA can share the SM with a collective CTA:
+    // at most 12 data vectors (48 registers) in flight next to the peer pointers.
+    static constexpr int U = NR == 1 ? 4 : NR == 2 ? 6 : NR == 3 ? 4 : NR == 4 ? 3 : 2;
     // allgather: one local source, NR destinations (pointers, not data, fill the registers)
     static constexpr int U_AG = NR <= 4 ? 4 : 2;
-    // shifted path keeps the neighbour's vector too
-    static constexpr int U_SH = NR <= 2 ? 4 : NR <= 4 ? 2 : 1;
+    // shifted path: same loads in flight as the aligned path plus the shuffled neighbour
+    static constexpr int U_SH = NR == 1 ? 4 : NR == 2 ? 4 : 2;
+    // ... of the bodies that also hold NR destination pointers (fused two-shot allreduce)
+    static constexpr int U_SH_PUSH = NR <= 6 ? U_SH : 1;
 };
 
 // ----------------------------------------------------------------------------
@@ -337,19 +346,6 @@ __device__ __forceinline__ uint4 shift_pair(const uint4 &a, const uint4 &b, unsi
                       __funnelshift_r(w3, w4, sh));
 }
 
-template <typename T, int NSRC>
-__device__ __forceinline__ uint4 load_sum(const uint4 *const (&s)[NSRC], size_t i) {
-    uint4 val[NSRC];
-#pragma unroll
-    for (int p = 0; p < NSRC; ++p) val[p] = ld_v4(s[p] + i);
-    if (NSRC == 1) return val[0];
-    Acc<T> acc;
-    acc.set(val[0]);
-#pragma unroll
-    for (int p = 1; p < NSRC; ++p) acc.add(val[p]);
-    return acc.pack();
-}
-
 template <typename T, int NSRC, int NDST, int U>
 __device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src, uint4 *const *dst, size_t nvec,
                                                          unsigned m, size_t tid, size_t nthr) {
@@ -359,66 +355,53 @@ __device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src
     for (int p = 0; p < NSRC; ++p) s[p] = src[p];
 #pragma unroll
     for (int q = 0; q < NDST; ++q) d[q] = dst[q];
-    const size_t bdim = blockDim.x, tile = (size_t)U * bdim;
-    const size_t cta = tid / bdim, nctas = nthr / bdim;
+    // A warp owns a run of 32*U aligned input vectors A[j0 .. j0+32U) and produces the 32*U - 1
+    // outputs that need only those: out[j] = shift(A[j], A[j+1]). A[j+1] comes from the right-hand
+    // lane by shuffle, for lane 31 from lane 0 of the next row; the run's last slot (row U-1,
+    // lane 31) has no right-hand neighbour and produces nothing — the next run starts ON that
+    // vector (runs overlap by one vector: 1/(32U) redundant loads, no extra registers, no
+    // divergent reload). Consecutive warps of a CTA take consecutive runs, CTAs stride by the grid.
+    constexpr size_t RUN = 32 * U - 1;
     const unsigned lane = threadIdx.x & 31u;
-    // whole warps walk the loop together (the shuffle needs every lane)
-    for (size_t t = cta; t * tile < nvec; t += nctas) {
-        const size_t base = t * tile + threadIdx.x;
-        // Phase 1: raw loads only, no use of a loaded value inside any branch (a use would make
-        // the warp wait for that round trip before issuing the next loads). Indices are clamped
-        // to nvec (A[nvec] is always readable) instead of predicated. Lane 31 also fetches the
-        // vector its right-hand neighbour would hold.
-        uint4 val[U][NSRC], xv[U][NSRC];
+    const size_t wpc = blockDim.x >> 5, warp = threadIdx.x >> 5;
+    const size_t cta = tid / blockDim.x, nctas = nthr / blockDim.x;
+    for (size_t r = cta * wpc + warp; r * RUN < nvec; r += nctas * wpc) { // warp-uniform trip count
+        const size_t j0 = r * RUN;
+        uint4 val[U][NSRC];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const size_t i = min(base + (size_t)u * bdim, nvec);
+            const size_t i = min(j0 + (size_t)u * 32 + lane, nvec); // A[nvec] is always readable
 #pragma unroll
             for (int p = 0; p < NSRC; ++p) val[u][p] = ld_v4(s[p] + i);
         }
-        if (lane == 31u) {
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const size_t i = min(base + (size_t)u * bdim + 1, nvec);
-#pragma unroll
-                for (int p = 0; p < NSRC; ++p) xv[u][p] = ld_v4(s[p] + i);
-            }
-        } else {
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-#pragma unroll
-                for (int p = 0; p < NSRC; ++p) xv[u][p] = make_uint4(0, 0, 0, 0);
-        }
-        // Phase 2: sums in rank order, neighbour exchange, shift, store
+        uint4 cur[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const size_t i = base + (size_t)u * bdim;
-            uint4 cur, ext;
             if (NSRC == 1) {
-                cur = val[u][0];
-                ext = xv[u][0];
+                cur[u] = val[u][0];
             } else {
-                Acc<T> a, b;
+                Acc<T> a;
                 a.set(val[u][0]);
-                b.set(xv[u][0]);
 #pragma unroll
-                for (int p = 1; p < NSRC; ++p) {
-                    a.add(val[u][p]);
-                    b.add(xv[u][p]);
-                }
-                cur = a.pack();
-                ext = b.pack();
+                for (int p = 1; p < NSRC; ++p) a.add(val[u][p]);
+                cur[u] = a.pack();
             }
-            uint4 nxt;
-            nxt.x = __shfl_down_sync(0xffffffffu, cur.x, 1);
-            nxt.y = __shfl_down_sync(0xffffffffu, cur.y, 1);
-            nxt.z = __shfl_down_sync(0xffffffffu, cur.z, 1);
-            nxt.w = __shfl_down_sync(0xffffffffu, cur.w, 1);
-            if (lane == 31u) nxt = ext;
-            if (i < nvec) {
-                const uint4 out = shift_pair(cur, nxt, m);
+        }
 #pragma unroll
-                for (int q = 0; q < NDST; ++q) st_v4(d[q] + i, out);
+        for (int u = 0; u < U; ++u) {
+            // lane l takes cur[u] of lane l+1; lane 31 takes cur[u+1] of lane 0
+            const uint4 give = (lane == 0 && u + 1 < U) ? cur[u + 1 < U ? u + 1 : u] : cur[u]; // (index clamped for the compiler only)
+            uint4 nxt;
+            nxt.x = __shfl_sync(0xffffffffu, give.x, (lane + 1) & 31);
+            nxt.y = __shfl_sync(0xffffffffu, give.y, (lane + 1) & 31);
+            nxt.z = __shfl_sync(0xffffffffu, give.z, (lane + 1) & 31);
+            nxt.w = __shfl_sync(0xffffffffu, give.w, (lane + 1) & 31);
+            const size_t j = j0 + (size_t)u * 32 + lane;
+            const bool last_slot = (u == U - 1) && lane == 31u;
+            if (j < nvec && !last_slot) {
+                const uint4 out = shift_pair(cur[u], nxt, m);
+#pragma unroll
+                for (int q = 0; q < NDST; ++q) st_v4(d[q] + j, out);
             }
         }
     }
@@ -521,7 +504,7 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
         src[p] = (const T *)v.send[p] + e0;
         dst[p] = (T *)v.recv[p] + e0;
     }
-    move_any<T, NR, NR, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, e1 - e0, cta, nctas);
+    move_any<T, NR, NR, Unroll<NR>::U, Unroll<NR>::U_SH_PUSH>(src, dst, e1 - e0, cta, nctas);
 
     cta_barrier<true>(v, e + 2, cta); // publishes the pushed slices
     cta_finish(v, e + 2, cta);
@@ -666,13 +649,105 @@ __device__ __forceinline__ void allreduce_multimem_body(const RankView &v, size_
             if (i < n) Multimem<T>::st(dst + i, val[u]);
         }
     }
-    // sub-vector tail (< 16 bytes): every rank reduces it for itself over the unicast mappings
+    // sub-vector tail (< 16 bytes): the last rank reduces it over the unicast mappings and pushes
+    // it into every recv (one reader-then-writer per element, like the slices: in-place safe)
     const size_t done = nvec * PV;
-    if (done < count && cta == 0) {
-        const T *ts[MAXR];
-        for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p] + done;
+    if (done < count && cta == 0 && v.rank == NR - 1) {
+        const T *ts[NR];
+        T *td[NR];
+#pragma unroll
+        for (int p = 0; p < NR; ++p) {
+            ts[p] = (const T *)v.send[p] + done;
+            td[p] = (T *)v.recv[p] + done;
+        }
+        reduce_store_elem<T>(ts, NR, td, NR, count - done, threadIdx.x, blockDim.x);
+    }
+
+    cta_barrier<true>(v, e + 2, cta); // publishes the multicast stores
+    cta_finish(v, e + 2, cta);
+}
+
+// ----------------------------------------------------------------------------
+// Reduce-scatter through the switch: rank r fetches ONLY its chunk with multimem.ld_reduce (the
+// switch pulls the chunk from all n ranks and adds) and stores it locally. Receive side: one
+// chunk instead of n-1; send side: n chunks leave every GPU. Needs 16-byte aligned chunks.
+// ----------------------------------------------------------------------------
+template <typename T, int NR>
+__device__ __forceinline__ void reduce_scatter_multimem_body(const RankView &v, size_t recvcount, int cta, int nctas) {
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
+
+    constexpr int PV = Elem<T>::PER_VEC;
+    constexpr int U = 8;
+    const size_t off = recvcount * (size_t)v.rank;
+    const size_t n = recvcount / PV;
+    const uint4 *src = (const uint4 *)((const T *)v.mc_send + off);
+    uint4 *dst = (uint4 *)v.recv[v.rank];
+    const size_t bdim = blockDim.x, tile = (size_t)U * bdim;
+    for (size_t t = cta; t * tile < n; t += nctas) {
+        const size_t base = t * tile + threadIdx.x;
+        uint4 val[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = base + (size_t)u * bdim;
+            if (i < n) val[u] = Multimem<T>::ld_reduce(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = base + (size_t)u * bdim;
+            if (i < n) st_v4(dst + i, val[u]);
+        }
+    }
+    const size_t done = n * PV;
+    if (done < recvcount && cta == 0) {
+        const T *ts[NR];
+#pragma unroll
+        for (int p = 0; p < NR; ++p) ts[p] = (const T *)v.send[p] + off + done;
         T *td[1] = {(T *)v.recv[v.rank] + done};
-        reduce_store_elem<T>(ts, NR, td, 1, count - done, threadIdx.x, blockDim.x);
+        reduce_store_elem<T>(ts, NR, td, 1, recvcount - done, threadIdx.x, blockDim.x);
+    }
+
+    cta_barrier<false>(v, e + 2, cta); // only reads of peer memory happened
+    cta_finish(v, e + 2, cta);
+}
+
+// ----------------------------------------------------------------------------
+// Allgather through the switch: read my shard once, ONE multimem.st per vector lands it in slot
+// `rank` of every rank's recv (the switch replicates). Send side: one shard instead of n-1.
+// ----------------------------------------------------------------------------
+template <typename T, int NR>
+__device__ __forceinline__ void allgather_multimem_body(const RankView &v, size_t sendcount, int cta, int nctas) {
+    const uint32_t e = cta_epoch(v, cta);
+    cta_barrier<false>(v, e + 1, cta);
+
+    constexpr int PV = Elem<T>::PER_VEC;
+    constexpr int U = 8;
+    const size_t off = sendcount * (size_t)v.rank;
+    const size_t n = sendcount / PV;
+    const uint4 *src = (const uint4 *)v.send[v.rank];
+    uint4 *dst = (uint4 *)((T *)v.mc_recv + off);
+    const size_t bdim = blockDim.x, tile = (size_t)U * bdim;
+    for (size_t t = cta; t * tile < n; t += nctas) {
+        const size_t base = t * tile + threadIdx.x;
+        uint4 val[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = base + (size_t)u * bdim;
+            if (i < n) val[u] = ld_v4(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = base + (size_t)u * bdim;
+            if (i < n) Multimem<T>::st(dst + i, val[u]);
+        }
+    }
+    const size_t done = n * PV;
+    if (done < sendcount && cta == 0) {
+        const T *ts[1] = {(const T *)v.send[v.rank] + done};
+        T *td[NR];
+#pragma unroll
+        for (int p = 0; p < NR; ++p) td[p] = (T *)v.recv[p] + off + done;
+        reduce_store_elem<T>(ts, 1, td, NR, sendcount - done, threadIdx.x, blockDim.x);
     }
 
     cta_barrier<true>(v, e + 2, cta); // publishes the multicast stores
@@ -683,7 +758,7 @@ __device__ __forceinline__ void allreduce_multimem_body(const RankView &v, size_
 // __global__ wrappers. Real mode: one rank per GPU, gridDim.y == 1. Emulation
 // mode: gridDim.y virtual ranks on one GPU in one cooperative launch.
 // ----------------------------------------------------------------------------
-enum Op { OP_AR1 = 0, OP_AR2 = 1, OP_AG = 2, OP_RS = 3, OP_ARM = 4, OP_A2A = 5 };
+enum Op { OP_AR1 = 0, OP_AR2 = 1, OP_AG = 2, OP_RS = 3, OP_ARM = 4, OP_A2A = 5, OP_RSM = 6, OP_AGM = 7 };
 
 template <typename T, int NR, int OP>
 __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta, int nctas) {
@@ -692,6 +767,8 @@ __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta,
     else if (OP == OP_AG) allgather_body<T, NR>(v, count, cta, nctas);
     else if (OP == OP_ARM) allreduce_multimem_body<T, NR>(v, count, cta, nctas);
     else if (OP == OP_A2A) alltoall_body<T, NR>(v, count, cta, nctas);
+    else if (OP == OP_RSM) reduce_scatter_multimem_body<T, NR>(v, count, cta, nctas);
+    else if (OP == OP_AGM) allgather_multimem_body<T, NR>(v, count, cta, nctas);
     else reduce_scatter_body<T, NR>(v, count, cta, nctas);
 }
 
@@ -699,15 +776,19 @@ __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta,
 // global load on the latency path). Real mode: one view, gridDim.y == 1. Emulation mode: one
 // view per virtual rank, gridDim.y == nranks, cooperative launch.
 // NR == 1 keeps <= 64 registers so two CTAs share an SM (the world-1 HBM copy wants the
-// occupancy), larger groups hold U*NR vectors in flight.
+// occupancy). NR > 1 is held to 96 registers: a 512-thread collective CTA then takes 48 K of the
+// SM's 64 K registers and leaves 16 K (and 1536 thread slots) to a CTA of the emulated compute,
+// so compute and communication share SMs instead of queueing for them (DESIGN: SM contention).
+#define DLNB_COLL_REGS(NR) ((NR) == 1 ? 64 : 96)
+
 template <typename T, int NR, int OP>
-__global__ void __launch_bounds__(512, (NR == 1 ? 2 : 1))
+__global__ void __maxnreg__(DLNB_COLL_REGS(NR))
 coll_kernel(const __grid_constant__ RankView v, size_t count) {
     run_op<T, NR, OP>(v, count, blockIdx.x, gridDim.x);
 }
 
 template <typename T, int NR, int OP>
-__global__ void __launch_bounds__(512, (NR == 1 ? 2 : 1))
+__global__ void __maxnreg__(DLNB_COLL_REGS(NR))
 coll_kernel_emu(const __grid_constant__ EmuViews ev, size_t count) {
     run_op<T, NR, OP>(ev.v[blockIdx.y], count, blockIdx.x, gridDim.x);
 }

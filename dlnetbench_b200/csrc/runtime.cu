@@ -161,10 +161,11 @@ struct dlnb_comm {
     std::vector<uint32_t> recv_seq;
     std::vector<char> slot_used;
     long ctas = 0, threads = 512, algo = DLNB_ALGO_AUTO, twoshot_min_bytes = -1 /* auto: 2 MiB / n */, timeout_ms = 30000,
-         multimem_min_bytes = 512 << 10;
+         multimem_min_bytes = 512 << 10, mc_ctas = 0 /* grid of the in-switch kernels; 0 = by group size */;
 };
 
 static constexpr int MAX_COMMS = 64;
+static constexpr int SYS_FLAG_SET = MAX_COMMS * 2; // one more set of flag rows / generations: the rank_sync barrier
 static constexpr size_t FLAG_BYTES_PER_COMM = (size_t)MAX_FLAG_CTAS * FLAG_ROW * sizeof(uint32_t);
 
 struct State {
@@ -178,6 +179,7 @@ struct State {
     long lanes = 2;
     cudaEvent_t ev_lane1 = nullptr, ev_excl = nullptr;
     uint32_t p2p_sent[MAXR] = {}, p2p_posted[MAXR] = {}; // messages sent to / receives posted for each world rank
+    uint32_t p2p_waited[MAXR] = {};                      // receives whose completion wait has been enqueued
     bool lane1_dirty = false, excl_pending = false, comm2_in_capture = false;
     cudaEvent_t ev_join = nullptr, ev_copy = nullptr, ev_iter0 = nullptr, ev_iter1 = nullptr, ev_tmp0 = nullptr,
                 ev_tmp1 = nullptr;
@@ -200,7 +202,9 @@ struct State {
     CommCtl *ctl = nullptr;    // symmetric allocation too (only used locally)
     uint32_t *host_error = nullptr, *host_error_dev = nullptr;
     int next_comm = 0;
+    std::vector<int> free_comm_ids; // ids of destroyed communicators (same order on every rank), reused after a reset
     std::vector<dlnb_comm *> comms;
+    long strict_barriers = 0, align_iterations = 1;
     // point-to-point mailboxes (symmetric, one per peer world rank) and sequence state (local)
     P2PBox *p2p_boxes = nullptr;
     P2PState *p2p_state = nullptr;
@@ -209,7 +213,12 @@ struct State {
     CommCtl *emu_ctl = nullptr;
     int emu_last_n = 0;
     // spin
-    long spin_ctas = 1, spin_threads = 32, slot_timing = 1, spin_slack_ns = 8000;
+    // footprint of the emulated compute: one 256-thread CTA on every SM, FMA-busy (spin_ctas 0 = one per SM)
+    long spin_ctas = 0, spin_threads = 256, spin_mode = SPIN_FMA, spin_smem = 0, slot_timing = 1, spin_slack_ns = 8000;
+    uint4 *spin_stream = nullptr; // SPIN_HBM: buffer larger than L2 that the spin kernel reads
+    size_t spin_stream_vecs = 0;
+    float *spin_sink = nullptr;
+    int spin_regs = 0;
     unsigned long long *spin_stamps = nullptr;
     unsigned spin_seq = 0;
     double spin_overhead_us = 0.0, spin_slope = 1.0;
@@ -535,13 +544,24 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     CU_TRY(cudaMalloc((void **)&G.d_scalar, sizeof(unsigned long long)));
     CU_TRY(cudaMalloc((void **)&G.spin_stamps, 2 * sizeof(unsigned long long)));
     CU_TRY(cudaMemset(G.spin_stamps, 0, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc((void **)&G.spin_sink, sizeof(float)));
+    {
+        cudaFuncAttributes fa;
+        CU_TRY(cudaFuncGetAttributes(&fa, spin_kernel));
+        G.spin_regs = fa.numRegs;
+    }
+    if (const char *v = getenv("DLNB_SPIN_MODE")) G.spin_mode = std::min(2L, std::max(0L, atol(v)));
+    if (const char *v = getenv("DLNB_SPIN_CTAS")) G.spin_ctas = std::max(0L, atol(v));
+    if (const char *v = getenv("DLNB_SPIN_THREADS")) G.spin_threads = std::min(1024L, std::max(32L, atol(v)));
+    if (const char *v = getenv("DLNB_STRICT_BARRIERS")) G.strict_barriers = atol(v) != 0;
+    if (const char *v = getenv("DLNB_ALIGN")) G.align_iterations = atol(v) != 0;
 
     G.inited = true;
     // first symmetric allocations: flag rows and control blocks of all communicators
     void *p = nullptr;
-    if (arena_alloc((size_t)MAX_COMMS * 2 * FLAG_BYTES_PER_COMM, &p)) { G.inited = false; return 1; } // x2: one set per lane
+    if (arena_alloc((size_t)(MAX_COMMS * 2 + 1) * FLAG_BYTES_PER_COMM, &p)) { G.inited = false; return 1; } // x2: one set per lane; +1: rank_sync
     G.flag_area = (char *)p;
-    if (arena_alloc((size_t)MAX_COMMS * 2 * sizeof(CommCtl), &p)) { G.inited = false; return 1; }
+    if (arena_alloc((size_t)(MAX_COMMS * 2 + 1) * sizeof(CommCtl), &p)) { G.inited = false; return 1; }
     G.ctl = (CommCtl *)p;
     if (arena_alloc((size_t)MAXR * sizeof(P2PBox), &p)) { G.inited = false; return 1; }
     G.p2p_boxes = (P2PBox *)p;
@@ -595,6 +615,8 @@ extern "C" int dlnb_finalize(void) {
     if (G.d_scalar) cudaFree(G.d_scalar);
     if (G.p2p_state) cudaFree(G.p2p_state);
     if (G.spin_stamps) cudaFree(G.spin_stamps);
+    if (G.spin_sink) cudaFree(G.spin_sink);
+    if (G.spin_stream) cudaFree(G.spin_stream);
     if (G.host_error) cudaFreeHost(G.host_error);
     cudaStreamDestroy(G.s_compute);
     cudaStreamDestroy(G.s_comm);
@@ -637,8 +659,24 @@ extern "C" int dlnb_symm_free(void *ptr) {
 
 extern "C" int dlnb_set(const char *key, long value) {
     if (!key) return fail("dlnb_set: null key");
-    if (!strcmp(key, "spin_ctas")) G.spin_ctas = std::max(1L, value);
+    if (!strcmp(key, "spin_ctas")) G.spin_ctas = std::max(0L, value); // 0 = one CTA per SM
     else if (!strcmp(key, "spin_threads")) G.spin_threads = std::min(1024L, std::max(1L, value));
+    else if (!strcmp(key, "spin_mode")) {
+        if (value < SPIN_SLEEP || value > SPIN_HBM) return fail("dlnb_set: spin_mode %ld not in 0..2", value);
+        if (value == SPIN_HBM && !G.spin_stream) {
+            NEED_INIT();
+            if (G.capturing) return fail("dlnb_set: spin_mode cannot change inside a graph capture");
+            G.spin_stream_vecs = ((size_t)1 << 30) / sizeof(uint4); // 1 GiB: eight times the L2
+            CU_TRY(cudaMalloc((void **)&G.spin_stream, G.spin_stream_vecs * sizeof(uint4)));
+            CU_TRY(cudaMemset(G.spin_stream, 0x11, G.spin_stream_vecs * sizeof(uint4)));
+        }
+        G.spin_mode = value;
+    } else if (!strcmp(key, "spin_smem")) {
+        if (value < 0 || value > 227 * 1024) return fail("dlnb_set: spin_smem %ld not in 0..232448", value);
+        if (value > 48 * 1024) CU_TRY(cudaFuncSetAttribute(spin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)value));
+        G.spin_smem = value;
+    } else if (!strcmp(key, "strict_barriers")) G.strict_barriers = value != 0;
+    else if (!strcmp(key, "align_iterations")) G.align_iterations = value != 0;
     else if (!strcmp(key, "slot_timing")) G.slot_timing = value;
     else if (!strcmp(key, "spin_slack_ns")) G.spin_slack_ns = std::max(0L, value);
     else if (!strcmp(key, "lanes")) G.lanes = value >= 2 ? 2 : 1;
@@ -647,8 +685,19 @@ extern "C" int dlnb_set(const char *key, long value) {
 }
 extern "C" long dlnb_get(const char *key) {
     if (!key) return -1;
-    if (!strcmp(key, "spin_ctas")) return G.spin_ctas;
+    if (!strcmp(key, "spin_ctas")) return G.spin_ctas > 0 ? G.spin_ctas : G.sms;
     if (!strcmp(key, "spin_threads")) return G.spin_threads;
+    if (!strcmp(key, "spin_mode")) return G.spin_mode;
+    if (!strcmp(key, "spin_smem")) return G.spin_smem;
+    if (!strcmp(key, "spin_regs")) return G.spin_regs;
+    if (!strcmp(key, "strict_barriers")) return G.strict_barriers;
+    if (!strcmp(key, "align_iterations")) return G.align_iterations;
+    // 1 when a CTA of the emulated compute and a 512-thread collective CTA (96 registers) fit on one SM together
+    if (!strcmp(key, "spin_coresident")) {
+        const long per_sm = ((G.spin_ctas > 0 ? G.spin_ctas : G.sms) + G.sms - 1) / G.sms;
+        const long regs = per_sm * G.spin_threads * ((G.spin_regs + 7) / 8 * 8);
+        return regs <= 65536 - 512 * 96 && per_sm * G.spin_threads <= 2048 - 512 && per_sm * G.spin_smem <= 227 * 1024;
+    }
     if (!strcmp(key, "slot_timing")) return G.slot_timing;
     if (!strcmp(key, "spin_slack_ns")) return G.spin_slack_ns;
     if (!strcmp(key, "sms")) return G.sms;
@@ -665,7 +714,9 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
     if (!ranks || !out) return fail("dlnb_comm_create: null argument");
     if (nranks < 1 || nranks > MAXR) return fail("dlnb_comm_create: group size %d not in 1..%d", nranks, MAXR);
     if (dtype < DLNB_F32 || dtype > DLNB_BF16) return fail("dlnb_comm_create: unknown dtype %d", dtype);
-    if (G.next_comm >= MAX_COMMS) return fail("dlnb_comm_create: more than %d communicators", MAX_COMMS);
+    if (G.next_comm >= MAX_COMMS && G.free_comm_ids.empty())
+        return fail("dlnb_comm_create: more than %d live communicators", MAX_COMMS);
+    if (G.capturing) return fail("dlnb_comm_create inside a graph capture");
     dlnb_comm *c = new dlnb_comm;
     c->me = -1;
     for (int i = 0; i < nranks; ++i) {
@@ -680,7 +731,20 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
         delete c;
         return fail("dlnb_comm_create: calling rank %d is not in the group", G.rank);
     }
-    c->id = G.next_comm++;
+    if (G.next_comm < MAX_COMMS) {
+        c->id = G.next_comm++;
+    } else {
+        // Reuse the flag rows of a destroyed communicator (creation and destruction are collective over
+        // the world in the same order, so every rank picks the same id). The rows and their generations
+        // carry the old group's history — and the new group may be another subset of ranks — so they
+        // restart from zero on every rank: everybody idle -> clear -> everybody cleared.
+        c->id = G.free_comm_ids.front();
+        G.free_comm_ids.erase(G.free_comm_ids.begin());
+        if (arena_sync_all_ranks()) { delete c; return 1; }
+        CU_TRY(cudaMemset(G.flag_area + (size_t)c->id * 2 * FLAG_BYTES_PER_COMM, 0, 2 * FLAG_BYTES_PER_COMM));
+        CU_TRY(cudaMemset(G.ctl + c->id * 2, 0, 2 * sizeof(CommCtl)));
+        if (arena_sync_all_ranks()) { delete c; return 1; }
+    }
     c->n = nranks;
     c->dtype = dtype;
     c->num_slots = std::max(1, num_slots);
@@ -705,14 +769,18 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
     if (const char *v = getenv("DLNB_ALGO")) c->algo = atol(v);
     if (const char *v = getenv("DLNB_TWOSHOT_MIN_BYTES")) c->twoshot_min_bytes = atol(v);
     if (const char *v = getenv("DLNB_MULTIMEM_MIN_BYTES")) c->multimem_min_bytes = atol(v);
+    if (const char *v = getenv("DLNB_MC_CTAS")) c->mc_ctas = atol(v);
     G.comms.push_back(c);
     *out = c;
     return 0;
 }
 extern "C" int dlnb_comm_destroy(dlnb_comm_t c) {
     if (!c) return 0;
+    bool live = false;
     for (auto &slot : G.comms)
-        if (slot == c) slot = nullptr;
+        if (slot == c) { slot = nullptr; live = true; }
+    if (!live) return fail("dlnb_comm_destroy: not a live communicator");
+    G.free_comm_ids.push_back(c->id);
     for (auto e : c->ev_start) cudaEventDestroy(e);
     for (auto e : c->ev_end) cudaEventDestroy(e);
     for (auto e : c->ev_done) cudaEventDestroy(e);
@@ -732,6 +800,7 @@ extern "C" int dlnb_comm_set(dlnb_comm_t c, const char *key, long value) {
     else if (!strcmp(key, "algo")) c->algo = value;
     else if (!strcmp(key, "twoshot_min_bytes")) c->twoshot_min_bytes = value;
     else if (!strcmp(key, "multimem_min_bytes")) c->multimem_min_bytes = value;
+    else if (!strcmp(key, "mc_ctas")) c->mc_ctas = value;
     else if (!strcmp(key, "timeout_ms")) c->timeout_ms = value;
     else return fail("dlnb_comm_set: unknown key %s", key);
     return 0;
@@ -743,6 +812,7 @@ extern "C" long dlnb_comm_get(dlnb_comm_t c, const char *key) {
     if (!strcmp(key, "algo")) return c->algo;
     if (!strcmp(key, "twoshot_min_bytes")) return c->twoshot_min_bytes;
     if (!strcmp(key, "multimem_min_bytes")) return c->multimem_min_bytes;
+    if (!strcmp(key, "mc_ctas")) return c->mc_ctas;
     if (!strcmp(key, "timeout_ms")) return c->timeout_ms;
     if (!strcmp(key, "id")) return c->id;
     return -1;
@@ -752,8 +822,10 @@ extern "C" long dlnb_comm_get(dlnb_comm_t c, const char *key) {
 // emulated compute
 // ---------------------------------------------------------------------------
 static int launch_spin(double ns) {
-    spin_kernel<<<(unsigned)G.spin_ctas, (unsigned)G.spin_threads, 0, G.s_compute>>>(
-        (unsigned long long)(ns + 0.5), G.spin_stamps, G.spin_seq++ & 1u, (unsigned long long)G.spin_slack_ns);
+    const unsigned ctas = (unsigned)(G.spin_ctas > 0 ? G.spin_ctas : G.sms);
+    spin_kernel<<<ctas, (unsigned)G.spin_threads, (size_t)G.spin_smem, G.s_compute>>>(
+        (unsigned long long)(ns + 0.5), G.spin_stamps, G.spin_seq++ & 1u, (unsigned long long)G.spin_slack_ns,
+        (int)G.spin_mode, G.spin_stream, G.spin_stream_vecs, G.spin_sink);
     CU_TRY(cudaGetLastError());
     G.launches++;
     G.compute_dirty = true;
@@ -832,25 +904,31 @@ static size_t work_bytes(int op, int n, size_t count, size_t esz) {
     case OP_AR1: return count * esz;
     case OP_AR2: return count * esz / (size_t)n;
     case OP_ARM: return count * esz / (size_t)n;
+    case OP_RSM: return count * esz;
+    case OP_AGM: return count * esz;
     case OP_A2A: return count * esz; // one block per peer, walked one after the other
     case OP_AG: return count * esz;
     default: return count * esz;
     }
 }
 
-static int pick_grid(long want, int dtype, int op, int n, int threads, size_t bytes, int *out) {
+static bool is_switch_op(int op) { return op == OP_ARM || op == OP_RSM || op == OP_AGM; }
+
+static int pick_grid(long want, long want_mc, int dtype, int op, int n, int threads, size_t bytes, int *out) {
     int occ = occupancy_dtype(dtype, op, n, threads);
     if (occ <= 0) return fail("collective kernel does not fit on an SM with %d threads", threads);
     // n > 1: every CTA waits on its peers' CTA of the same index, so all must be resident;
     // n == 1: no barriers, and 4 CTAs per SM (two waves at occupancy 2) measured best for HBM
     int cap = n == 1 ? G.sms * 16 : std::min(G.sms * occ, MAX_FLAG_CTAS);
     long g;
-    if (want > 0) {
+    if (want > 0 && !(is_switch_op(op) && want_mc > 0)) {
         g = want;
     } else if (n == 1) {
         g = (long)G.sms * 4;
-    } else if (op == OP_ARM) {
-        g = 16; // the switch does the adding: 16 CTAs saturate the links (measured: more is slower)
+    } else if (is_switch_op(op)) {
+        // the switch does the adding / replicating: few CTAs saturate the links. Measured (profiles/):
+        // 16 CTAs best on 8 GPUs (more is slower), 32 on 4 (16 leaves a quarter of the rate unused)
+        g = want_mc > 0 ? want_mc : (n >= 8 ? 16 : 32);
     } else {
         g = 128; // NVLink-bound peer loads/stores: measured best for >= 64 MB, harmless below
     }
@@ -914,14 +992,14 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
     if (count && (!send || !recv)) return fail("null buffer");
     const size_t esz = dtype_size(c->dtype);
     char *mc_s = nullptr, *mc_r = nullptr;
+    const bool mc_possible = c->n > 1 && c->n == G.world && G.mc_enabled; // the multicast object spans every rank
     if (op == OP_AR1 || op == OP_AR2) {
         const size_t bytes = count * esz;
         // measured cross-over (B200): one-shot wins up to ~1 MiB on 2 GPUs, ~256 KiB on 8
         const size_t two_min = c->twoshot_min_bytes >= 0 ? (size_t)c->twoshot_min_bytes : (size_t)(2 << 20) / (size_t)c->n;
         const bool small = two_min > bytes;
-        // in-switch reduction needs the multicast view of both buffers, the whole world in the
-        // group (the multicast object spans every rank) and 16-byte aligned buffers
-        if (c->n > 1 && c->n == G.world && G.mc_enabled && (c->algo == DLNB_ALGO_MULTIMEM || c->algo == DLNB_ALGO_AUTO) &&
+        // in-switch reduction needs the multicast view of both buffers and 16-byte aligned buffers
+        if (mc_possible && (c->algo == DLNB_ALGO_MULTIMEM || c->algo == DLNB_ALGO_AUTO) &&
             (((uintptr_t)send | (uintptr_t)recv) & 15) == 0) {
             mc_s = translate_mc(send);
             mc_r = translate_mc(recv);
@@ -935,13 +1013,32 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
         else if (c->algo == DLNB_ALGO_MULTIMEM) op = OP_ARM;
         else if (mc_ok && c->n >= 4 && bytes >= (size_t)c->multimem_min_bytes) op = OP_ARM; // n < 4: P2P moves fewer bytes
         else op = (c->n == 1 || small) ? OP_AR1 : OP_AR2;
+        // In place (MPI_IN_PLACE / ncclAllReduce with sendbuff == recvbuff): the one-shot kernel has every
+        // rank read all of its peers' send buffers while each rank writes its own recv, so a peer could
+        // read an element that is already a sum. The two-shot and in-switch kernels read and write every
+        // element through its one owner: they are in-place safe.
+        if (op == OP_AR1 && c->n > 1) {
+            const char *s0 = (const char *)send, *r0 = (const char *)recv;
+            if (s0 < r0 + bytes && r0 < s0 + bytes) op = OP_AR2;
+        }
+    } else if ((op == OP_AG || op == OP_RS) && c->algo == DLNB_ALGO_MULTIMEM && c->n > 1) {
+        // in-switch variants on request only (AUTO stays on the P2P kernels, see DESIGN: the byte count on
+        // the busier direction does not shrink). Chunks that are not 16-byte aligned keep the P2P path.
+        if (!mc_possible)
+            return fail("multimem %s requested but unavailable (multicast %s, group %d of world %d)", op == OP_AG ? "allgather" : "reduce-scatter",
+                        G.mc_enabled ? "on" : "off", c->n, G.world);
+        if ((((uintptr_t)send | (uintptr_t)recv) & 15) == 0 && (count * esz) % 16 == 0) {
+            if (op == OP_AG) mc_r = translate_mc(recv); else mc_s = translate_mc(send);
+            if (op == OP_AG && mc_r) op = OP_AGM;
+            else if (op == OP_RS && mc_s) op = OP_RSM;
+        }
     }
     // Grid first: it decides the lane. Small allreduces (<= 64 CTAs, so two of them plus the spin
     // kernel are always co-resident) alternate between the two lanes; everything else is
     // exclusive on lane 0.
     int grid = 1;
     const int threads = (int)c->threads;
-    if (count && pick_grid(c->ctas, c->dtype, op, c->n, threads, work_bytes(op, c->n, count, esz), &grid)) return 1;
+    if (count && pick_grid(c->ctas, c->mc_ctas, c->dtype, op, c->n, threads, work_bytes(op, c->n, count, esz), &grid)) return 1;
     const bool is_ar = op == OP_AR1 || op == OP_AR2 || op == OP_ARM;
     // up to 8 MiB the grid makes no measurable difference (26.2 / 26.5 / 26.1 us at 4 MiB with 32 / 64 /
     // 128 CTAs on 8 GPUs): keep such allreduces at <= 64 CTAs so that they can use the lanes
@@ -973,8 +1070,9 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
             v.recv[i] = r;
             v.flags[i] = (uint32_t *)translate(G.flag_area + (size_t)(c->id * 2 + lane) * FLAG_BYTES_PER_COMM, c->ranks[i]);
         }
-        v.mc_send = op == OP_ARM ? mc_s : nullptr;
-        v.mc_recv = op == OP_ARM ? mc_r : nullptr;
+        v.mc_send = is_switch_op(op) ? mc_s : nullptr;
+        v.mc_recv = is_switch_op(op) ? mc_r : nullptr;
+        v.strict = (int)G.strict_barriers;
         v.ctl = G.ctl + (c->id * 2 + lane);
         v.host_error = G.host_error_dev;
         v.timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;
@@ -984,8 +1082,11 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
     }
     if (lane == 1) G.lane1_dirty = true;
     else if (!laned && mark_exclusive_on_lane0()) return 1;
-    if (G.capturing) { // completion is the graph's: nothing for the host to wait on per slot
-        c->slot_used[slot] = 0;
+    if (G.capturing) {
+        // no host-side completion inside a capture; the event lets Wait / WaitAll / the blocking calls
+        // order the COMPUTE stream behind this collective, as the host's blocking did (dlnb_wait)
+        CU_TRY(cudaEventRecord(c->ev_done[slot], st));
+        c->slot_used[slot] = 1;
         c->slot_timed[slot] = 0;
         return 0;
     }
@@ -1023,20 +1124,34 @@ extern "C" int dlnb_alltoall(dlnb_comm_t c, const void *send, void *recv, size_t
 static int finish_recv(dlnb_comm *c, int slot);
 extern "C" int dlnb_wait(dlnb_comm_t c, int slot) {
     NEED_INIT();
-    if (G.capturing) return 0; // ordering inside a captured iteration is the streams'; the host waits on the replay
     if (!c) return fail("null communicator");
     if (slot == -1) slot = c->num_slots;
     else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
     if (!c->slot_used[slot]) return 0;
+    if (G.capturing) {
+        // The host cannot block inside a capture. What its blocking meant for the schedule — nothing
+        // enqueued afterwards (the next emulated compute) starts before this collective is done —
+        // becomes a device-side edge: the compute stream waits for the collective's completion event.
+        CU_TRY(cudaStreamWaitEvent(G.s_compute, c->ev_done[slot], 0));
+        c->slot_used[slot] = 0;
+        return 0;
+    }
     if (finish_recv(c, slot)) return 1;
     CU_TRY(cudaEventSynchronize(c->ev_done[slot]));
     return check_watchdog();
 }
 extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
     NEED_INIT();
-    if (G.capturing) return 0;
     if (!c) return fail("null communicator");
     if (nslots > c->num_slots) nslots = c->num_slots;
+    if (G.capturing) { // see dlnb_wait: the compute stream waits for every outstanding slot
+        for (int i = 0; i < nslots; ++i)
+            if (c->slot_used[i]) {
+                CU_TRY(cudaStreamWaitEvent(G.s_compute, c->ev_done[i], 0));
+                c->slot_used[i] = 0;
+            }
+        return 0;
+    }
     // the communication stream is ordered: waiting for the newest used slot suffices,
     // but slots may have been recorded in any order, so wait for each.
     for (int i = 0; i < nslots; ++i)
@@ -1047,9 +1162,14 @@ extern "C" int dlnb_waitall(dlnb_comm_t c, int nslots) {
 }
 extern "C" int dlnb_barrier(dlnb_comm_t c) {
     NEED_INIT();
-    if (G.capturing) return 0;
     if (!c) return fail("null communicator");
     if (drain_lane1_into_lane0()) return 1; // both lanes: lane 0 finishes after whatever lane 1 has in flight
+    if (G.capturing) { // device-side form of "the host waits for the communication stream"
+        if (!G.comm_in_capture) return 0; // nothing captured on it yet
+        CU_TRY(cudaEventRecord(G.ev_join, G.s_comm));
+        CU_TRY(cudaStreamWaitEvent(G.s_compute, G.ev_join, 0));
+        return 0;
+    }
     CU_TRY(cudaStreamSynchronize(G.s_comm));
     return check_watchdog();
 }
@@ -1117,6 +1237,10 @@ static int p2p(dlnb_comm *c, bool is_send, const void *buf, size_t count, int pe
         c->recv_src[slot] = -1;
     } else {
         const unsigned long long off = (unsigned long long)(b - (const char *)G.window[G.rank]);
+        // the sender polls post[seq % P2P_RING]: a receive posted P2P_RING ahead of one that has not been
+        // waited for would overwrite the word its sender may still be looking for
+        if (G.p2p_posted[wpeer] - G.p2p_waited[wpeer] >= (uint32_t)P2P_RING)
+            return fail("Irecv: %d receives from rank %d are already outstanding (wait for one first)", P2P_RING, wpeer);
         const uint32_t seq = ++G.p2p_posted[wpeer];
         recv_post_kernel<<<1, 32, 0, G.s_comm>>>(theirs, seq, off);
         CU_TRY(cudaGetLastError());
@@ -1141,6 +1265,7 @@ static int finish_recv(dlnb_comm *c, int slot) {
     if (mark_exclusive_on_lane0()) return 1;
     if (c->slot_timed[slot]) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
     CU_TRY(cudaEventRecord(c->ev_done[slot], G.s_comm));
+    G.p2p_waited[c->recv_src[slot]]++;
     c->recv_src[slot] = -1;
     return 0;
 }
@@ -1158,6 +1283,26 @@ extern "C" int dlnb_recv(dlnb_comm_t c, void *buf, size_t count, int source) {
 // ---------------------------------------------------------------------------
 // device timing of one proxy iteration (both streams)
 // ---------------------------------------------------------------------------
+// One flag barrier between all world ranks, enqueued on `st` (dlnb_set "align_iterations", default on).
+static int launch_rank_sync(cudaStream_t st) {
+    if (G.world <= 1 || !G.align_iterations) return 0;
+    RankView v;
+    memset(&v, 0, sizeof(v));
+    v.rank = G.rank;
+    v.nranks = G.world;
+    for (int r = 0; r < G.world; ++r) {
+        v.flags[r] = (uint32_t *)translate(G.flag_area + (size_t)SYS_FLAG_SET * FLAG_BYTES_PER_COMM, r);
+        if (!v.flags[r]) return fail("rank sync: flag rows of rank %d are not mapped", r);
+    }
+    v.ctl = G.ctl + SYS_FLAG_SET;
+    v.host_error = G.host_error_dev;
+    v.timeout_ns = 30ull * 1000000000ull;
+    rank_sync_kernel<<<1, 32, 0, st>>>(v);
+    CU_TRY(cudaGetLastError());
+    G.launches++;
+    return 0;
+}
+
 extern "C" int dlnb_iter_begin(void) {
     NEED_INIT();
     if (G.capturing) return fail("dlnb_iter_begin inside a graph capture (time the replay instead)");
@@ -1165,6 +1310,11 @@ extern "C" int dlnb_iter_begin(void) {
     if (drain_lane1_into_lane0()) return 1;
     CU_TRY(cudaEventRecord(G.ev_join, G.s_comm));
     CU_TRY(cudaStreamWaitEvent(G.s_compute, G.ev_join, 0));
+    // ... on every rank at the same moment (one flag round trip apart): the reference's ranks leave an
+    // MPI_Barrier together before each timed run (dp.cpp:259, fsdp.cpp:391); here the ranks' compute
+    // streams do, so the spin chains of all ranks run in step and a collective is not charged for the
+    // time a late rank needs to arrive
+    if (launch_rank_sync(G.s_compute)) return 1;
     CU_TRY(cudaEventRecord(G.ev_iter0, G.s_compute));
     CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_iter0, 0));
     CU_TRY(cudaStreamWaitEvent(G.s_comm2, G.ev_iter0, 0));
@@ -1181,6 +1331,7 @@ extern "C" int dlnb_batch_begin(void) {
     G.copy_dirty = true;
     if (join_streams()) return 1;
     if (drain_lane1_into_lane0()) return 1;
+    if (launch_rank_sync(G.s_comm)) return 1; // all ranks start the batch together
     CU_TRY(cudaEventRecord(G.ev_iter0, G.s_comm));
     CU_TRY(cudaStreamWaitEvent(G.s_comm2, G.ev_iter0, 0));
     return 0;
@@ -1238,6 +1389,8 @@ extern "C" int dlnb_graph_end(dlnb_graph_t *out) {
     G.capturing = G.comm_in_capture = G.comm2_in_capture = false;
     G.compute_dirty = G.copy_dirty = false;
     G.lane1_dirty = G.excl_pending = false;
+    for (dlnb_comm *c : G.comms) // slots recorded inside the capture have no host-side completion
+        if (c) std::fill(c->slot_used.begin(), c->slot_used.end(), 0);
     if (e != cudaSuccess || e2 != cudaSuccess || !g->graph) {
         delete g;
         return fail("graph capture failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
@@ -1374,6 +1527,45 @@ extern "C" int dlnb_verify_sum_pattern(const void *ptr, size_t count, size_t ele
     return 0;
 }
 
+extern "C" int dlnb_verify_sum_pattern_tol(const void *ptr, size_t count, size_t elem_offset, int dtype, int kind, uint64_t seed,
+                                           const int *ranks, int nranks, double rel_tol, uint64_t *mismatches, double *worst_rel_err) {
+    NEED_INIT();
+    if (drain_lane1_into_lane0()) return 1;
+    if (!mismatches || !ranks || nranks < 1 || nranks > MAXR) return fail("bad argument");
+    RankList rl;
+    rl.n = nranks;
+    for (int i = 0; i < nranks; ++i) rl.r[i] = ranks[i];
+    static unsigned *d_worst = nullptr;
+    if (!d_worst) CU_TRY(cudaMalloc((void **)&d_worst, sizeof(unsigned)));
+    CU_TRY(cudaMemsetAsync(G.d_scalar, 0, sizeof(unsigned long long), G.s_comm));
+    CU_TRY(cudaMemsetAsync(d_worst, 0, sizeof(unsigned), G.s_comm));
+    if (count) {
+        const int g = aux_grid(count);
+        const float tol = (float)rel_tol;
+        if (dtype == DLNB_F32)
+            verify_sum_tol_kernel<float><<<g, 256, 0, G.s_comm>>>((const float *)ptr, count, elem_offset, kind, seed, rl, tol, G.d_scalar, d_worst);
+        else if (dtype == DLNB_F16)
+            verify_sum_tol_kernel<__half><<<g, 256, 0, G.s_comm>>>((const __half *)ptr, count, elem_offset, kind, seed, rl, tol, G.d_scalar, d_worst);
+        else if (dtype == DLNB_BF16)
+            verify_sum_tol_kernel<__nv_bfloat16><<<g, 256, 0, G.s_comm>>>((const __nv_bfloat16 *)ptr, count, elem_offset, kind, seed, rl, tol, G.d_scalar, d_worst);
+        else return fail("unknown dtype %d", dtype);
+        CU_TRY(cudaGetLastError());
+        G.launches++;
+    }
+    unsigned long long h = 0;
+    unsigned w = 0;
+    CU_TRY(cudaMemcpyAsync(&h, G.d_scalar, sizeof(h), cudaMemcpyDeviceToHost, G.s_comm));
+    CU_TRY(cudaMemcpyAsync(&w, d_worst, sizeof(w), cudaMemcpyDeviceToHost, G.s_comm));
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    *mismatches = h;
+    if (worst_rel_err) {
+        float f;
+        memcpy(&f, &w, sizeof(f));
+        *worst_rel_err = f;
+    }
+    return 0;
+}
+
 extern "C" int dlnb_checksum(const void *ptr, size_t bytes, uint64_t *out) {
     NEED_INIT();
     if (drain_lane1_into_lane0()) return 1; // helper kernels run on lane 0 and must see lane 1's results
@@ -1412,6 +1604,7 @@ extern "C" int dlnb_flush_l2(void) {
 // ---------------------------------------------------------------------------
 static int emu(int op, int nranks, const void *const *send, void *const *recv, size_t count, int dtype, int ctas) {
     NEED_INIT();
+    if (G.capturing) return fail("emu calls synchronise the stream: not usable between dlnb_graph_begin and dlnb_graph_end");
     if (nranks < 1 || nranks > MAXR) return fail("emu: nranks %d not in 1..%d", nranks, MAXR);
     if (!send || !recv) return fail("emu: null buffer list");
     if (!count) return 0;
@@ -1442,6 +1635,7 @@ static int emu(int op, int nranks, const void *const *send, void *const *recv, s
         v.ctl = G.emu_ctl + r;
         v.host_error = G.host_error_dev;
         v.timeout_ns = 10ull * 1000000000ull;
+        v.strict = (int)G.strict_barriers;
     }
     const int threads = 512;
     int occ = occupancy_dtype(dtype, op, nranks, threads);
@@ -1476,6 +1670,39 @@ extern "C" int dlnb_emu_alltoall(int nranks, const void *const *send, void *cons
     return emu(OP_A2A, nranks, send, recv, sendcount, dtype, ctas);
 }
 
+// Point-to-point on ONE GPU: the receive-post, send and receive-wait kernels of dlnb_irecv / dlnb_isend /
+// dlnb_wait run in stream order against one mailbox that plays both ends (the receiver posts into the
+// "sender's" box, the sender publishes "done" into the "receiver's": the fields are disjoint). The posted
+// offset is the absolute address of `recv` against a null window base. Same device code as the
+// multi-GPU path, so the one-GPU test box exercises the rendezvous, the shifted mover and the last-CTA
+// completion count.
+extern "C" int dlnb_emu_sendrecv(const void *send, void *recv, size_t count, int dtype, int ctas) {
+    NEED_INIT();
+    if (G.capturing) return fail("emu calls synchronise the stream: not usable between dlnb_graph_begin and dlnb_graph_end");
+    if (dtype < DLNB_F32 || dtype > DLNB_BF16) return fail("emu_sendrecv: unknown dtype %d", dtype);
+    if (count && (!send || !recv)) return fail("emu_sendrecv: null buffer");
+    if (G.world != 1) return fail("emu_sendrecv is the one-GPU test vehicle (world size 1)");
+    const size_t bytes = count * dtype_size(dtype);
+    static uint32_t seq = 0;
+    ++seq;
+    P2PBox *box = G.p2p_boxes; // slot 0: unused by a world of one
+    if (drain_lane1_into_lane0()) return 1;
+    recv_post_kernel<<<1, 32, 0, G.s_comm>>>(box, seq, (unsigned long long)(uintptr_t)recv);
+    CU_TRY(cudaGetLastError());
+    const size_t vecs = bytes / 16 + 1;
+    long g = ctas > 0 ? ctas : 64;
+    g = std::min<long>(g, std::max<long>(1, (long)((vecs + 511) / 512)));
+    g = std::min<long>(g, G.sms);
+    send_kernel<<<(unsigned)g, 512, 0, G.s_comm>>>(box, box, (char *)nullptr, send, bytes, G.p2p_state, 0, seq, 10ull * 1000000000ull,
+                                                    G.host_error_dev);
+    CU_TRY(cudaGetLastError());
+    recv_wait_kernel<<<1, 32, 0, G.s_comm>>>(box, seq, 10ull * 1000000000ull, G.host_error_dev);
+    CU_TRY(cudaGetLastError());
+    G.launches += 3;
+    CU_TRY(cudaStreamSynchronize(G.s_comm));
+    return check_watchdog();
+}
+
 // ---------------------------------------------------------------------------
 // dlnb_emu_allreduce_noalloc — the emulated n-rank allreduce for callers that may not allocate
 // ---------------------------------------------------------------------------
@@ -1502,6 +1729,8 @@ static unsigned char *g_noalloc_dev_ptr[64] = {};
 extern "C" int dlnb_emu_allreduce_noalloc(int nranks, const void *const *send, void *const *recv, size_t count,
                                           int dtype, int algo, int ctas) {
     NEED_INIT();
+    if (G.capturing)
+        return fail("emu_allreduce_noalloc synchronises the stream: not usable between dlnb_graph_begin and dlnb_graph_end");
     if (nranks < 1 || nranks > MAXR) return fail("emu_allreduce_noalloc: nranks %d not in 1..%d", nranks, MAXR);
     if (!send || !recv) return fail("emu_allreduce_noalloc: null buffer list");
     if (dtype < DLNB_F32 || dtype > DLNB_BF16) return fail("emu_allreduce_noalloc: unknown dtype %d", dtype);

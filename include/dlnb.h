@@ -92,15 +92,17 @@ size_t dlnb_symm_bytes_in_use(void);
  * MPI_FLOAT, num_requests)` and MPI_Comm_split / ncclCommSplit
  * (proxy_classes.hpp:55-64,138-147; fsdp.cpp:258-283). `ranks` lists the world
  * ranks of the group in group order; must contain the caller. Collective over the
- * WORLD (every world rank creates its communicators in the same order). A process
- * may create at most 64 communicators between dlnb_init and dlnb_finalize: each owns
- * a set of flag rows whose generations live on, so a destroyed communicator's set is
- * not handed out again (the proxies create one to three). */
+ * WORLD (every world rank creates and destroys its communicators in the same order).
+ * At most 64 communicators are alive at a time: each owns a set of flag rows. Once 64
+ * have been created, dlnb_comm_create reuses the rows of a destroyed communicator after
+ * resetting them on every rank (all ranks idle -> clear -> all ranks cleared). */
 int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int dtype, dlnb_comm_t *out);
 int dlnb_comm_destroy(dlnb_comm_t c);
 int dlnb_comm_rank(dlnb_comm_t c);
 int dlnb_comm_size(dlnb_comm_t c);
-/* tuning knobs: "ctas" (CTAs per collective kernel), "threads", "algo" (dlnb_algo),
+/* tuning knobs: "ctas" (CTAs per collective kernel), "mc_ctas" (the same for the in-switch
+ * kernels; 0 = 16 on 8 ranks, 32 below), "threads", "algo" (dlnb_algo; DLNB_ALGO_MULTIMEM also
+ * sends allgather / reduce-scatter through the switch where the chunks are 16-byte aligned),
  * "twoshot_min_bytes" / "multimem_min_bytes" (AUTO thresholds), "timeout_ms" (flag-spin watchdog). */
 int dlnb_comm_set(dlnb_comm_t c, const char *key, long value);
 long dlnb_comm_get(dlnb_comm_t c, const char *key);
@@ -117,8 +119,18 @@ int dlnb_compute_sync(void);
  * %globaltimer rate (applied to every request), `overhead_us` = start-up latency of an
  * isolated spin (reported, not subtracted). */
 int dlnb_spin_calibrate(double *overhead_us, double *slope);
-/* "spin_ctas" / "spin_threads": footprint of the spin kernel (SM share of the emulated
- * compute); "spin_slack_ns": chaining window; "slot_timing": record a start event per slot;
+/* Footprint of the emulated compute — what a collective has to share the GPU with:
+ *   "spin_ctas" (0 = one CTA per SM, the default), "spin_threads" (default 256),
+ *   "spin_mode" 0 = sleep (__nanosleep back-off: resident, issues nothing), 1 = FMA-busy
+ *   (default: four dependent FMA chains per thread), 2 = HBM-busy (streams a 1 GiB buffer),
+ *   "spin_smem" (dynamic shared memory per CTA, ballast only).
+ *   dlnb_get("spin_coresident") = 1 when one spin CTA per SM leaves room for a collective CTA
+ *   (512 threads x 96 registers) on the same SM; dlnb_get("spin_regs") = registers per thread.
+ * "align_iterations" (default 1): dlnb_iter_begin / dlnb_batch_begin run one flag barrier between
+ * all ranks on the device, so that every rank's iteration starts within a flag round trip.
+ * "strict_barriers" (default 0): 1 = every flag barrier uses st.release.sys / ld.acquire.sys
+ * (0: the barriers that publish no peer writes use relaxed flag traffic).
+ * "spin_slack_ns": chaining window; "slot_timing": record a start event per slot;
  * "lanes" (1 or 2, default 2; all ranks alike): with 2, consecutive small allreduces (grid
  * <= 64 CTAs) alternate between two ordered communication streams with their own flag rows so
  * that their barrier latencies overlap; allgather, reduce-scatter and large allreduces are
@@ -131,7 +143,10 @@ long dlnb_get(const char *key);
  * collective cannot start before "its" backward finished — this replaces the host
  * ordering usleep → Iallreduce of the reference. `slot` is the reference's
  * `index` (request / stream id). */
-/* ProxyCommunicator::Iallreduce (proxy_classes.hpp:32,66-68,149-152) */
+/* ProxyCommunicator::Iallreduce (proxy_classes.hpp:32,66-68,149-152). send == recv (in place, as
+ * MPI_IN_PLACE / ncclAllReduce allow) is supported: overlapping buffers take the two-shot or the
+ * in-switch kernel, where each element is read and written by one owner. Allgather,
+ * reduce-scatter and all-to-all buffers must not overlap. */
 int dlnb_iallreduce(dlnb_comm_t c, const void *send, void *recv, size_t count, int slot);
 /* ProxyCommunicator::Iallgather (proxy_classes.hpp:34-35,91-93,202-204); recvcount==sendcount */
 int dlnb_iallgather(dlnb_comm_t c, const void *send, void *recv, size_t sendcount, int slot);
@@ -156,7 +171,7 @@ int dlnb_ialltoall(dlnb_comm_t c, const void *send, void *recv, size_t sendcount
  * been delivered (send) / has arrived (recv). dlnb_irecv only posts the receive; the kernel that
  * waits for the data is enqueued by dlnb_wait / dlnb_waitall, so a posted receive never sits in
  * front of a send the peer is waiting for (Irecv + Isend rings are safe). At most 8 receives
- * from one source may be outstanding. Needs the VMM arena (world > 1); not capturable. */
+ * from one source may be outstanding (posted and not yet waited for): the 9th dlnb_irecv fails. Needs the VMM arena (world > 1); not capturable. */
 int dlnb_send(dlnb_comm_t c, const void *buf, size_t count, int dest);
 int dlnb_recv(dlnb_comm_t c, void *buf, size_t count, int source);
 int dlnb_isend(dlnb_comm_t c, const void *buf, size_t count, int dest, int slot);
@@ -185,8 +200,12 @@ int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms);
  * Added (no reference counterpart). For launch-bound configurations (vit_h with 4000 buckets:
  * 9 us of compute per bucket against ~30 us of host launch work) one proxy iteration —
  * every dlnb_compute_spin and collective issued between begin and end — is captured once and
- * replayed with a single launch. Inside a capture dlnb_wait / dlnb_waitall / dlnb_barrier /
- * dlnb_compute_sync return at once (the streams keep the order); after dlnb_graph_launch the
+ * replayed with a single launch. Inside a capture the host cannot block, so dlnb_wait /
+ * dlnb_waitall / dlnb_barrier and the blocking collectives turn their blocking into a
+ * device-side edge: the compute stream waits for the collective's completion event, i.e.
+ * compute issued afterwards starts only when that collective is done — the schedule the
+ * host-blocking calls produce outside a capture (fsdp: the backward of unit u-1 starts after
+ * the ReduceScatter of unit u). dlnb_compute_sync returns at once. After dlnb_graph_launch the
  * host waits with dlnb_compute_sync() or dlnb_iter_end(). The kernels keep their barrier
  * generations and spin stamps in device memory, so a replay needs no patched arguments.
  * All ranks must capture the same sequence and launch the same number of replays. */
@@ -210,6 +229,13 @@ int dlnb_fill_pattern(void *ptr, size_t count, int dtype, int kind, uint64_t see
  * `ranks` of pattern(kind, seed, r, elem_offset + i), rounded once to dtype. */
 int dlnb_verify_sum_pattern(const void *ptr, size_t count, size_t elem_offset, int dtype, int kind,
                             uint64_t seed, const int *ranks, int nranks, uint64_t *mismatches);
+/* Tolerance form, for reductions whose summation order is the NVSwitch's and not ours (DLNB_ALGO_MULTIMEM):
+ * counts elements with |got - ref| > rel_tol * sum_r |x_r| + half an ulp of the dtype at |ref|, where ref is
+ * the rank-order fp32 sum; SURVEY 8c pin (2) sets rel_tol = 2 (n-1) eps. `worst_rel_err` (may be NULL)
+ * receives the largest |got - ref| / sum_r |x_r| seen. */
+int dlnb_verify_sum_pattern_tol(const void *ptr, size_t count, size_t elem_offset, int dtype, int kind,
+                                uint64_t seed, const int *ranks, int nranks, double rel_tol,
+                                uint64_t *mismatches, double *worst_rel_err);
 /* order-independent 64-bit checksum of a device buffer (sum of mixed 32-bit words) */
 int dlnb_checksum(const void *ptr, size_t bytes, uint64_t *out);
 /* writes a buffer larger than L2 (timing hygiene between timed iterations) */
@@ -228,6 +254,11 @@ int dlnb_emu_reduce_scatter(int nranks, const void *const *send, void *const *re
                             size_t recvcount, int dtype, int ctas);
 int dlnb_emu_alltoall(int nranks, const void *const *send, void *const *recv, size_t sendcount,
                       int dtype, int ctas);
+/* send / recv (proxy_classes.hpp:103-117,211-227) on one GPU: the receive-post, send and
+ * receive-wait kernels of dlnb_irecv / dlnb_isend / dlnb_wait in stream order against one mailbox
+ * that plays both ends; `count` elements of `dtype` go from `send` to `recv` (any alignment).
+ * World size 1 only. */
+int dlnb_emu_sendrecv(const void *send, void *recv, size_t count, int dtype, int ctas);
 
 /* ---- the emulated allreduce for callers that cannot allocate -----------------------
  * No counterpart in the reference (it has no such constraint: every backend there allocates
@@ -240,7 +271,9 @@ int dlnb_emu_alltoall(int nranks, const void *const *send, void *const *recv, si
  *   - limit: at most 64 CTAs per virtual rank (`ctas` 0 = default 16); a larger request is
  *     refused with an error, nothing is launched. nranks 1..8 as elsewhere.
  *   - the first call on a device looks up the array's device address (cudaGetSymbolAddress);
- *     make that first call before starting any stream capture.
+ *     make that first call before starting any stream capture. Between dlnb_graph_begin and
+ *     dlnb_graph_end this entry point (like every dlnb_emu_* call) returns an error: it
+ *     synchronises the communication stream.
  *   - all calls share the one array and it keeps the last call's contents; each call clears it
  *     on the communication stream before launching. Calls that overlap on the GPU would race
  *     on it: issue them one after another (the entry point returns after its kernel has
