@@ -26,6 +26,8 @@ constexpr Device device = Device::GPU;
 static b200::HostTimer timer_allgather, timer_reduce_scatter, timer_allgather_wait_fwd, timer_allgather_wait_bwd,
     timer_barrier, timer_runtime;
 static bool blocking_compute = false;
+static bool in_graph_capture = false;
+static float first_allgather_ms = 0.f; // device time of the exposed Allgather of unit 0 (most recent iteration)
 
 static inline void emulate_compute(float usec) {
     b200::check(dlnb_compute_spin((double)(uint64_t)usec), "compute spin"); // usleep(float) truncates
@@ -44,6 +46,7 @@ void run_fsdp(Tensor<T, device> **shard_params, Tensor<T, device> *layer_params,
     timer_allgather.start();
     unit_comm->Allgather(shard_params[0]->data, shard_count(0), layer_params->data, shard_count(0));
     timer_allgather.stop();
+    if (!in_graph_capture) first_allgather_ms = static_cast<B200Communicator *>(unit_comm)->slot_ms(-1);
 
     // forward: gather unit u+1 while unit u computes (the last unit's forward is not emulated,
     // as in the reference: U-1 sleeps)
@@ -179,6 +182,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
                     num_units, sharding_factor, max_params_per_shard.data(), num_replicas, unit_comm_proxy,
                     allreduce_comm_proxy);
     };
+    in_graph_capture = cli.graph; // slot times are not host-visible inside a captured iteration
     auto iteration = b200::make_runner(plain_iteration, cli.graph);
     std::vector<float> warmup_times;
     for (int i = 0; i < cli.warmup; i++) {
@@ -270,6 +274,9 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         .put("ratio_to_lower_bound", lower_bound_us ? b200::median(device_ms_max) * 1000.0 / (double)lower_bound_us : 0.0)
         .put("reduce_scatter_last_ms", last_rs_ms)
         .put("reduce_scatter_busbw_GBps", rs_bus)
+        .put("allgather_first_ms", first_allgather_ms)
+        .put("allgather_busbw_GBps", first_allgather_ms <= 0 ? 0.0 : F > 1 ? (double)(F - 1) / F * (double)allgather_msg_size / (first_allgather_ms * 1e-3) / 1e9
+                                                            : 2.0 * (double)reducescatter_msg_size / (first_allgather_ms * 1e-3) / 1e9)
         .put("spin_overhead_us", spin_overhead_us)
         .put("spin_slope", spin_slope)
         .put("spin_ctas", (long)dlnb_get("spin_ctas"))

@@ -95,6 +95,8 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_iter_begin": (i, []),
         "dlnb_iter_end": (i, [C.POINTER(C.c_float)]),
         "dlnb_batch_begin": (i, []),
+        "dlnb_batch_begin_concurrent": (i, [C.c_double]),
+        "dlnb_batch_end": (i, [C.POINTER(C.c_float)]),
         "dlnb_graph_begin": (i, []),
         "dlnb_graph_end": (i, [pvp]),
         "dlnb_graph_launch": (i, [vp]),
@@ -105,6 +107,8 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_memcpy_d2h": (i, [vp, vp, sz]),
         "dlnb_memcpy_h2d_async": (i, [vp, vp, sz]),
         "dlnb_memcpy_d2h_async": (i, [vp, vp, sz]),
+        "dlnb_memcpy_h2d_after_compute": (i, [vp, vp, sz]),
+        "dlnb_memcpy_d2h_after_slot": (i, [vp, i, vp, vp, sz]),
         "dlnb_host_alloc": (i, [sz, pvp]),
         "dlnb_host_free": (i, [vp]),
         "dlnb_fill_pattern": (i, [vp, sz, i, i, u64, i]),
@@ -313,6 +317,16 @@ def compute_sync() -> None:
 
 def batch_begin() -> None:
     check(lib().dlnb_batch_begin())
+
+
+def batch_begin_concurrent(gate_us: float = 0.0) -> None:
+    check(lib().dlnb_batch_begin_concurrent(float(gate_us)))
+
+
+def batch_end() -> float:
+    ms = C.c_float()
+    check(lib().dlnb_batch_end(C.byref(ms)))
+    return ms.value
 
 
 def set_option(key: str, value: int) -> None:

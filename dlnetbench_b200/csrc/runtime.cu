@@ -173,7 +173,9 @@ struct State {
     int rank = 0, world = 1, device = 0, sms = 0;
     ArenaKind kind = ARENA_LOCAL;
     Bootstrap boot;
-    cudaStream_t s_compute = nullptr, s_comm = nullptr, s_comm2 = nullptr, s_copy = nullptr;
+    cudaStream_t s_compute = nullptr, s_comm = nullptr, s_comm2 = nullptr, s_copy = nullptr, s_out = nullptr;
+    cudaEvent_t ev_gate = nullptr, ev_out = nullptr;
+    bool out_dirty = false; // device -> host copies enqueued on s_out that the end of the iteration must wait for
     // Two communication lanes: consecutive small allreduces alternate between s_comm (lane 0) and
     // s_comm2 (lane 1) so their barrier latencies overlap; everything else runs on lane 0 alone.
     long lanes = 2;
@@ -184,6 +186,7 @@ struct State {
     cudaEvent_t ev_join = nullptr, ev_copy = nullptr, ev_iter0 = nullptr, ev_iter1 = nullptr, ev_tmp0 = nullptr,
                 ev_tmp1 = nullptr;
     bool compute_dirty = false, copy_dirty = false;
+    bool detach_compute = false; // between dlnb_batch_begin_concurrent and dlnb_batch_end: collectives do not wait for compute
     bool capturing = false, comm_in_capture = false; // between dlnb_graph_begin and dlnb_graph_end
     // arena
     std::vector<Chunk> chunks;
@@ -532,6 +535,9 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     CU_TRY(cudaEventCreateWithFlags(&G.ev_excl, cudaEventDisableTiming));
     if (const char *v = getenv("DLNB_LANES")) G.lanes = atol(v) >= 2 ? 2 : 1;
     CU_TRY(cudaStreamCreateWithPriority(&G.s_copy, cudaStreamNonBlocking, lo));
+    CU_TRY(cudaStreamCreateWithPriority(&G.s_out, cudaStreamNonBlocking, lo));
+    CU_TRY(cudaEventCreateWithFlags(&G.ev_gate, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&G.ev_out, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&G.ev_join, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&G.ev_copy, cudaEventDisableTiming));
     CU_TRY(cudaEventCreate(&G.ev_iter0));
@@ -542,8 +548,8 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     *G.host_error = 0;
     CU_TRY(cudaHostGetDevicePointer((void **)&G.host_error_dev, G.host_error, 0));
     CU_TRY(cudaMalloc((void **)&G.d_scalar, sizeof(unsigned long long)));
-    CU_TRY(cudaMalloc((void **)&G.spin_stamps, 2 * sizeof(unsigned long long)));
-    CU_TRY(cudaMemset(G.spin_stamps, 0, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc((void **)&G.spin_stamps, 4 * sizeof(unsigned long long))); // [0,1] compute chain, [2,3] gate spins
+    CU_TRY(cudaMemset(G.spin_stamps, 0, 4 * sizeof(unsigned long long)));
     CU_TRY(cudaMalloc((void **)&G.spin_sink, sizeof(float)));
     {
         cudaFuncAttributes fa;
@@ -624,6 +630,9 @@ extern "C" int dlnb_finalize(void) {
     cudaEventDestroy(G.ev_lane1);
     cudaEventDestroy(G.ev_excl);
     cudaStreamDestroy(G.s_copy);
+    cudaStreamDestroy(G.s_out);
+    cudaEventDestroy(G.ev_gate);
+    cudaEventDestroy(G.ev_out);
     cudaEventDestroy(G.ev_join);
     cudaEventDestroy(G.ev_copy);
     cudaEventDestroy(G.ev_iter0);
@@ -947,7 +956,7 @@ static int join_streams() {
         G.compute_dirty = true;
         G.comm_in_capture = true;
     }
-    if (G.compute_dirty) {
+    if (G.compute_dirty && !G.detach_compute) {
         CU_TRY(cudaEventRecord(G.ev_join, G.s_compute));
         CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_join, 0));
         if (G.lanes > 1) {
@@ -1319,6 +1328,7 @@ extern "C" int dlnb_iter_begin(void) {
     CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_iter0, 0));
     CU_TRY(cudaStreamWaitEvent(G.s_comm2, G.ev_iter0, 0));
     CU_TRY(cudaStreamWaitEvent(G.s_copy, G.ev_iter0, 0));
+    CU_TRY(cudaStreamWaitEvent(G.s_out, G.ev_iter0, 0));
     return 0;
 }
 extern "C" int dlnb_batch_begin(void) {
@@ -1336,6 +1346,33 @@ extern "C" int dlnb_batch_begin(void) {
     CU_TRY(cudaStreamWaitEvent(G.s_comm2, G.ev_iter0, 0));
     return 0;
 }
+// Contention measurements: a batch of collectives timed on the communication stream WHILE emulated compute that was
+// enqueued before runs beside it — between these two calls collectives do not wait for the compute stream.
+extern "C" int dlnb_batch_begin_concurrent(double gate_us) {
+    NEED_INIT();
+    if (G.capturing) return fail("dlnb_batch_begin_concurrent inside a graph capture");
+    if (drain_lane1_into_lane0()) return 1;
+    G.detach_compute = true;
+    if (gate_us > 0) { // one sleeping warp holds the communication stream while the host queues the batch behind it
+        spin_kernel<<<1, 32, 0, G.s_comm>>>((unsigned long long)(gate_us * 1000.0), G.spin_stamps + 2, 0u, 0ull, (int)SPIN_SLEEP, nullptr, 0, G.spin_sink);
+        CU_TRY(cudaGetLastError());
+        G.launches++;
+    }
+    if (launch_rank_sync(G.s_comm)) return 1;
+    CU_TRY(cudaEventRecord(G.ev_iter0, G.s_comm));
+    CU_TRY(cudaStreamWaitEvent(G.s_comm2, G.ev_iter0, 0));
+    return 0;
+}
+extern "C" int dlnb_batch_end(float *ms) {
+    NEED_INIT();
+    if (G.capturing) return fail("dlnb_batch_end inside a graph capture");
+    if (drain_lane1_into_lane0()) return 1;
+    CU_TRY(cudaEventRecord(G.ev_iter1, G.s_comm));
+    CU_TRY(cudaEventSynchronize(G.ev_iter1));
+    if (ms) CU_TRY(cudaEventElapsedTime(ms, G.ev_iter0, G.ev_iter1));
+    G.detach_compute = false;
+    return check_watchdog();
+}
 extern "C" int dlnb_iter_end(float *ms) {
     NEED_INIT();
     if (G.capturing) return fail("dlnb_iter_end inside a graph capture (time the replay instead)");
@@ -1343,6 +1380,11 @@ extern "C" int dlnb_iter_end(float *ms) {
     G.copy_dirty = true;
     if (join_streams()) return 1;
     if (drain_lane1_into_lane0()) return 1;
+    if (G.out_dirty) { // results on their way to the host belong to the iteration
+        CU_TRY(cudaEventRecord(G.ev_out, G.s_out));
+        CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_out, 0));
+        G.out_dirty = false;
+    }
     CU_TRY(cudaEventRecord(G.ev_iter1, G.s_comm));
     CU_TRY(cudaEventSynchronize(G.ev_iter1));
     if (ms) CU_TRY(cudaEventElapsedTime(ms, G.ev_iter0, G.ev_iter1));
@@ -1466,6 +1508,30 @@ extern "C" int dlnb_memcpy_d2h_async(void *dst, const void *src, size_t bytes) {
     if (drain_lane1_into_lane0()) return 1;
     CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, G.s_comm));
     if (mark_exclusive_on_lane0()) return 1;
+    return 0;
+}
+// End-to-end path of the bench: a bucket's gradients come from pinned host memory once "its" backward slice
+// (the compute enqueued so far) has finished — not earlier, so the copies are not prefetched under the forward —
+// and the reduced bucket goes back to the host as soon as its collective (slot) is done, on a stream of its own
+// so that the copy engines and the communication stream do not queue behind one another.
+extern "C" int dlnb_memcpy_h2d_after_compute(void *dst, const void *src, size_t bytes) {
+    NEED_INIT();
+    if (G.capturing) return fail("dlnb_memcpy_h2d_after_compute inside a graph capture");
+    CU_TRY(cudaEventRecord(G.ev_gate, G.s_compute));
+    CU_TRY(cudaStreamWaitEvent(G.s_copy, G.ev_gate, 0));
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, G.s_copy));
+    G.copy_dirty = true;
+    return 0;
+}
+extern "C" int dlnb_memcpy_d2h_after_slot(dlnb_comm_t c, int slot, void *dst, const void *src, size_t bytes) {
+    NEED_INIT();
+    if (G.capturing) return fail("dlnb_memcpy_d2h_after_slot inside a graph capture");
+    if (!c) return fail("null communicator");
+    if (slot < 0 || slot >= c->num_slots || !c->slot_used[slot]) return fail("slot %d has no recorded collective", slot);
+    if (finish_recv(c, slot)) return 1;
+    CU_TRY(cudaStreamWaitEvent(G.s_out, c->ev_done[slot], 0));
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, G.s_out));
+    G.out_dirty = true;
     return 0;
 }
 extern "C" int dlnb_host_alloc(size_t bytes, void **ptr) {

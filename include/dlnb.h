@@ -192,6 +192,11 @@ int dlnb_iter_end(float *ms);
  * enqueued so far (e.g. a long spin): times a pre-queued batch of collectives on the device
  * with the host out of the loop. Stop with dlnb_iter_end(). */
 int dlnb_batch_begin(void);
+/* Contention measurements: like dlnb_batch_begin / dlnb_iter_end, but the collectives issued between the two
+ * calls do NOT wait for the compute stream — emulated compute enqueued before keeps running beside them — and
+ * the end does not wait for it either. */
+int dlnb_batch_begin_concurrent(double gate_us); /* gate_us > 0: a sleeping warp holds the stream that long while the host queues */
+int dlnb_batch_end(float *ms);
 /* device time of the most recent collective recorded in `slot` (ms); slot -1 = the most
  * recent BLOCKING call (those use an internal slot, never one of the caller's) */
 int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms);
@@ -221,6 +226,12 @@ int dlnb_memcpy_d2h(void *dst, const void *src, size_t bytes);
 /* asynchronous copies on the communication stream from/to pinned host memory */
 int dlnb_memcpy_h2d_async(void *dst, const void *src, size_t bytes);
 int dlnb_memcpy_d2h_async(void *dst, const void *src, size_t bytes);
+/* End-to-end path (no reference counterpart: the reference never moves its buffers). H2D on the copy
+ * stream once the compute enqueued so far has finished ("this bucket's gradients exist when its backward
+ * slice ends"); the next collective waits for it. D2H of a result on a stream of its own as soon as the
+ * collective recorded in `slot` is done; dlnb_iter_end() waits for it. Pinned host memory (dlnb_host_alloc). */
+int dlnb_memcpy_h2d_after_compute(void *dst, const void *src, size_t bytes);
+int dlnb_memcpy_d2h_after_slot(dlnb_comm_t c, int slot, void *dst, const void *src, size_t bytes);
 int dlnb_host_alloc(size_t bytes, void **ptr);
 int dlnb_host_free(void *ptr);
 /* x[i] = pattern(kind, seed, as_rank, i), i in [0,count) */
