@@ -25,6 +25,11 @@ def main():
     ap.add_argument("--algo", type=int, default=0)
     ap.add_argument("--threads", type=int, default=512)
     ap.add_argument("--out", default="")
+    ap.add_argument("--mc-ctas", default="0", help="grid(s) of the in-switch kernels (comma list, 0 = default by group size)")
+    ap.add_argument("--counts", default="", help="explicit element counts per rank message (comma list) instead of the size ladder; "
+                                                  "for allgather / reduce_scatter: the SHARD count (e.g. 110240167, the odd llama3_70b shard)")
+    ap.add_argument("--nvlink", action="store_true", help="NVML link counters around each batch: measured bytes per launch per direction")
+    ap.add_argument("--strict", type=int, default=0, help="1: st.release / ld.acquire on every flag barrier")
     ap.add_argument("--per-slot", dest="b2b", action="store_false", help="busBW from per-launch slot events instead of the back-to-back batch")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", os.environ.get("DLNB_RANK", 0)))
@@ -35,6 +40,16 @@ def main():
     comm = capi.B200Communicator(list(range(world)), num_slots=a.iters, dtype=dt)
     comm.set("algo", a.algo)
     comm.set("threads", a.threads)
+    capi.set_option("strict_barriers", a.strict)
+    links = None
+    if a.nvlink:
+        from dlnetbench_b200 import nvlink
+
+        links = nvlink.LinkCounters(int(os.environ.get("LOCAL_RANK", os.environ.get("DLNB_LOCAL_RANK", rank))))
+        if not links.ok:
+            if rank == 0:
+                print(json.dumps({"nvlink_counters_unavailable": links.why}), flush=True)
+            links = None
     # ring of buffers larger than L2 so no iteration finds its input cached
     nxt, prv = (rank + 1) % world, (rank - 1) % world
 
@@ -50,22 +65,31 @@ def main():
             comm.Isend(s.data, sc, nxt, i)
 
     rows = []
+    ladder = []
     size = a.min_bytes
-    while size <= a.max_bytes:
+    while size <= a.max_bytes and not a.counts:
+        ladder.append((size, None))
+        size *= 4
+    for c in [int(x) for x in a.counts.split(",") if x]:
+        ladder.append((c * esz * (1 if a.op in ("allreduce", "sendrecv") else world), c))
+    for size, shard in ladder:
         count = size // esz
         if a.op in ("allreduce", "sendrecv"):
             sc, rc = count, count
         elif a.op == "allgather":
-            sc, rc = count // world, (count // world) * world
+            sc = shard if shard else count // world
+            rc = sc * world
         else:
-            sc, rc = (count // world) * world, count // world
+            rc = shard if shard else count // world
+            sc = rc * world
         nbuf = max(2, min(a.iters, (300 << 20) // max(size, 1) + 1))
         send = [capi.Tensor(max(sc, 1), dt) for _ in range(nbuf)]
         recv = [capi.Tensor(max(rc, 1), dt) for _ in range(nbuf)]
         for t in send:
             t.fill(capi.PAT_INT, 0, rank)
-        for ctas in [int(c) for c in a.ctas.split(",")]:
+        for ctas, mc_ctas in [(int(c), int(m)) for c in a.ctas.split(",") for m in a.mc_ctas.split(",")]:
             comm.set("ctas", ctas)
+            comm.set("mc_ctas", mc_ctas)
             for rep in range(2):  # first pass = warm-up
                 for i in range(a.iters):
                     issue(send[i % nbuf], recv[i % nbuf], sc, rc, i)
@@ -74,11 +98,17 @@ def main():
             # device-only batch time: a spin blocks the communication stream while the host queues
             # the whole batch (no per-slot timing events), one event pair around the batch
             capi.set_option("slot_timing", 0)
+            before = links.settle() if links else None
             capi.compute_spin(max(3000.0, 40.0 * a.iters))
             capi.batch_begin()
             for i in range(a.iters):
                 issue(send[i % nbuf], recv[i % nbuf], sc, rc, i)
             b2b = capi.iter_end() / a.iters
+            wire = None
+            if links:
+                from dlnetbench_b200 import nvlink
+
+                wire = nvlink.per_launch(before, links.settle(), a.iters)
             capi.set_option("slot_timing", 1)
             med = b2b if a.b2b else ms[len(ms) // 2]
             if world == 1:
@@ -90,11 +120,16 @@ def main():
             else:
                 bus = (world - 1) / world * max(sc, rc) * esz / (med * 1e-3) / 1e9
             row = dict(op=a.op, dtype=a.dtype, world=world, bytes=sc * esz if a.op != "reduce_scatter" else sc * esz,
-                       ctas=ctas, us=med * 1e3, us_slot_med=ms[len(ms) // 2] * 1e3, us_b2b=b2b * 1e3, busbw_GBps=bus)
+                       ctas=ctas, mc_ctas=mc_ctas, algo=a.algo, us=med * 1e3, us_slot_med=ms[len(ms) // 2] * 1e3, us_b2b=b2b * 1e3, busbw_GBps=bus)
+            if wire:
+                row.update({k: round(v) for k, v in wire.items()})
+                row["nvlink_tx_GBps"] = wire["data_tx_bytes_per_launch"] / (b2b * 1e-3) / 1e9
+                row["nvlink_rx_GBps"] = wire["data_rx_bytes_per_launch"] / (b2b * 1e-3) / 1e9
             rows.append(row)
             if rank == 0:
                 print(json.dumps(row), flush=True)
-        size *= 4
+        for t in send + recv:
+            t.free()
     if rank == 0 and a.out:
         json.dump(rows, open(a.out, "w"), indent=1)
     capi.finalize()
