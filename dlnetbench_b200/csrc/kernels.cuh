@@ -46,6 +46,7 @@ struct RankView {
     uint32_t *host_error;      // mapped pinned word, set by the watchdog (may be null)
     unsigned long long timeout_ns;
     int strict;                // 1: every barrier uses release/acquire flag traffic (see cta_barrier)
+    int shift_overlap;         // shifted mover: runs overlap by 1, 2 or 8 vectors (16 B / one 32 B sector / one 128 B line)
 };
 
 struct EmuViews {
@@ -348,29 +349,32 @@ __device__ __forceinline__ uint4 shift_pair(const uint4 &a, const uint4 &b, unsi
 
 template <typename T, int NSRC, int NDST, int U>
 __device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src, uint4 *const *dst, size_t nvec,
-                                                         unsigned m, size_t tid, size_t nthr) {
+                                                         unsigned m, size_t tid, size_t nthr, unsigned overlap) {
     const uint4 *s[NSRC];
     uint4 *d[NDST];
 #pragma unroll
     for (int p = 0; p < NSRC; ++p) s[p] = src[p];
 #pragma unroll
     for (int q = 0; q < NDST; ++q) d[q] = dst[q];
-    // A warp owns a run of 32*U aligned input vectors A[j0 .. j0+32U) and produces the 32*U - 1
-    // outputs that need only those: out[j] = shift(A[j], A[j+1]). A[j+1] comes from the right-hand
-    // lane by shuffle, for lane 31 from lane 0 of the next row; the run's last slot (row U-1,
-    // lane 31) has no right-hand neighbour and produces nothing — the next run starts ON that
-    // vector (runs overlap by one vector: 1/(32U) redundant loads, no extra registers, no
-    // divergent reload). Consecutive warps of a CTA take consecutive runs, CTAs stride by the grid.
-    constexpr size_t RUN = 32 * U - 1;
+    // A warp owns a window of 32*U aligned input vectors A[base .. base+32U) and produces the outputs that need
+    // only those: out[j] = shift(A[j], A[j+1]). A[j+1] comes from the right-hand lane by shuffle, for lane 31
+    // from lane 0 of the next row. Consecutive windows OVERLAP by `overlap` vectors (1, 2 or 8: the last output
+    // of a window needs the first vector of the next), so nothing is reloaded by a divergent lane and no extra
+    // registers are held; with 2 / 8 every window starts on a 32-byte sector / 128-byte line of the sources
+    // (a 512-byte warp load then touches 4 lines, not 5) at the price of 2 / 8 vectors loaded twice per window.
+    // Consecutive warps of a CTA take consecutive windows, CTAs stride by the grid.
+    const long long run = 32 * U - (long long)overlap;
+    const long long a0 = overlap > 1 ? (long long)(((uintptr_t)s[0] >> 4) & (overlap - 1)) : 0;
     const unsigned lane = threadIdx.x & 31u;
-    const size_t wpc = blockDim.x >> 5, warp = threadIdx.x >> 5;
-    const size_t cta = tid / blockDim.x, nctas = nthr / blockDim.x;
-    for (size_t r = cta * wpc + warp; r * RUN < nvec; r += nctas * wpc) { // warp-uniform trip count
-        const size_t j0 = r * RUN;
+    const long long wpc = blockDim.x >> 5, warp = threadIdx.x >> 5;
+    const long long cta = (long long)(tid / blockDim.x), nctas = (long long)(nthr / blockDim.x);
+    const long long nv = (long long)nvec;
+    for (long long r = cta * wpc + warp; r * run - a0 < nv; r += nctas * wpc) { // warp-uniform trip count
+        const long long base = r * run - a0;
         uint4 val[U][NSRC];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const size_t i = min(j0 + (size_t)u * 32 + lane, nvec); // A[nvec] is always readable
+            const long long i = min(max(base + u * 32 + (long long)lane, 0ll), nv); // A[nvec] is always readable
 #pragma unroll
             for (int p = 0; p < NSRC; ++p) val[u][p] = ld_v4(s[p] + i);
         }
@@ -396,9 +400,8 @@ __device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src
             nxt.y = __shfl_sync(0xffffffffu, give.y, (lane + 1) & 31);
             nxt.z = __shfl_sync(0xffffffffu, give.z, (lane + 1) & 31);
             nxt.w = __shfl_sync(0xffffffffu, give.w, (lane + 1) & 31);
-            const size_t j = j0 + (size_t)u * 32 + lane;
-            const bool last_slot = (u == U - 1) && lane == 31u;
-            if (j < nvec && !last_slot) {
+            const long long slot = u * 32 + (long long)lane, j = base + slot;
+            if (slot < run && j >= 0 && j < nv) {
                 const uint4 out = shift_pair(cur[u], nxt, m);
 #pragma unroll
                 for (int q = 0; q < NDST; ++q) st_v4(d[q] + j, out);
@@ -416,7 +419,7 @@ __device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src
 // 128-bit path, the last few elements element-wise.
 // ----------------------------------------------------------------------------
 template <typename T, int NSRC, int NDST, int U, int USH>
-__device__ __forceinline__ void move_any(const T *const *src, T *const *dst, size_t count, int cta, int nctas) {
+__device__ __forceinline__ void move_any(const T *const *src, T *const *dst, size_t count, int cta, int nctas, unsigned overlap = 8) {
     const size_t tid = (size_t)cta * blockDim.x + threadIdx.x;
     const size_t nthr = (size_t)nctas * blockDim.x;
     constexpr int PV = Elem<T>::PER_VEC;
@@ -444,7 +447,7 @@ __device__ __forceinline__ void move_any(const T *const *src, T *const *dst, siz
 #pragma unroll
         for (int q = 0; q < NDST; ++q) vd[q] = (uint4 *)(dst[q] + head);
         if (m == 0) reduce_store_vec<T, NSRC, NDST, U, NSRC == 1 && NDST == 1>(vs, vd, nvec, tid, nthr);
-        else reduce_store_vec_shifted<T, NSRC, NDST, USH>(vs, vd, nvec, m, tid, nthr);
+        else reduce_store_vec_shifted<T, NSRC, NDST, USH>(vs, vd, nvec, m, tid, nthr, overlap == 1 || overlap == 2 ? overlap : 8u);
     }
     // head and tail: a handful of elements, one CTA
     if (cta == 0) {
@@ -475,7 +478,7 @@ __device__ __forceinline__ void allreduce_oneshot_body(const RankView &v, size_t
 #pragma unroll
     for (int p = 0; p < NR; ++p) src[p] = (const T *)v.send[p];
     T *dst[1] = {(T *)v.recv[v.rank]};
-    move_any<T, NR, 1, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, count, cta, nctas);
+    move_any<T, NR, 1, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, count, cta, nctas, v.shift_overlap);
 
     cta_barrier<false>(v, e + 2, cta); // only reads happened
     cta_finish(v, e + 2, cta);
@@ -504,7 +507,7 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
         src[p] = (const T *)v.send[p] + e0;
         dst[p] = (T *)v.recv[p] + e0;
     }
-    move_any<T, NR, NR, Unroll<NR>::U, Unroll<NR>::U_SH_PUSH>(src, dst, e1 - e0, cta, nctas);
+    move_any<T, NR, NR, Unroll<NR>::U, Unroll<NR>::U_SH_PUSH>(src, dst, e1 - e0, cta, nctas, v.shift_overlap);
 
     cta_barrier<true>(v, e + 2, cta); // publishes the pushed slices
     cta_finish(v, e + 2, cta);
@@ -524,7 +527,7 @@ __device__ __forceinline__ void allgather_body(const RankView &v, size_t sendcou
     T *dst[NR];
 #pragma unroll
     for (int p = 0; p < NR; ++p) dst[p] = (T *)v.recv[p] + off;
-    move_any<T, 1, NR, Unroll<NR>::U_AG, Unroll<NR>::U_SH>(src, dst, sendcount, cta, nctas);
+    move_any<T, 1, NR, Unroll<NR>::U_AG, Unroll<NR>::U_SH>(src, dst, sendcount, cta, nctas, v.shift_overlap);
 
     cta_barrier<true>(v, e + 2, cta); // publishes the pushed shard
     cta_finish(v, e + 2, cta);
@@ -545,7 +548,7 @@ __device__ __forceinline__ void reduce_scatter_body(const RankView &v, size_t re
 #pragma unroll
     for (int p = 0; p < NR; ++p) src[p] = (const T *)v.send[p] + off;
     T *dst[1] = {(T *)v.recv[v.rank]};
-    move_any<T, NR, 1, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, recvcount, cta, nctas);
+    move_any<T, NR, 1, Unroll<NR>::U, Unroll<NR>::U_SH>(src, dst, recvcount, cta, nctas, v.shift_overlap);
 
     cta_barrier<false>(v, e + 2, cta); // only reads happened
     cta_finish(v, e + 2, cta);
@@ -567,7 +570,7 @@ __device__ __forceinline__ void alltoall_body(const RankView &v, size_t sendcoun
         const int p = (v.rank + 1 + k) % NR;
         const T *src[1] = {(const T *)v.send[v.rank] + (size_t)p * sendcount};
         T *dst[1] = {(T *)v.recv[p] + (size_t)v.rank * sendcount};
-        move_any<T, 1, 1, 4, 4>(src, dst, sendcount, cta, nctas);
+        move_any<T, 1, 1, 4, 4>(src, dst, sendcount, cta, nctas, v.shift_overlap);
     }
 
     cta_barrier<true>(v, e + 2, cta); // publishes the pushed blocks

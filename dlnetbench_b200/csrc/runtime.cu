@@ -207,7 +207,7 @@ struct State {
     int next_comm = 0;
     std::vector<int> free_comm_ids; // ids of destroyed communicators (same order on every rank), reused after a reset
     std::vector<dlnb_comm *> comms;
-    long strict_barriers = 0, align_iterations = 1;
+    long strict_barriers = 0, align_iterations = 1, shift_overlap = 8;
     // point-to-point mailboxes (symmetric, one per peer world rank) and sequence state (local)
     P2PBox *p2p_boxes = nullptr;
     P2PState *p2p_state = nullptr;
@@ -561,6 +561,7 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     if (const char *v = getenv("DLNB_SPIN_THREADS")) G.spin_threads = std::min(1024L, std::max(32L, atol(v)));
     if (const char *v = getenv("DLNB_STRICT_BARRIERS")) G.strict_barriers = atol(v) != 0;
     if (const char *v = getenv("DLNB_ALIGN")) G.align_iterations = atol(v) != 0;
+    if (const char *v = getenv("DLNB_SHIFT_OVERLAP")) { const long o = atol(v); if (o == 1 || o == 2 || o == 8) G.shift_overlap = o; }
 
     G.inited = true;
     // first symmetric allocations: flag rows and control blocks of all communicators
@@ -686,6 +687,10 @@ extern "C" int dlnb_set(const char *key, long value) {
         G.spin_smem = value;
     } else if (!strcmp(key, "strict_barriers")) G.strict_barriers = value != 0;
     else if (!strcmp(key, "align_iterations")) G.align_iterations = value != 0;
+    else if (!strcmp(key, "shift_overlap")) {
+        if (value != 1 && value != 2 && value != 8) return fail("dlnb_set: shift_overlap must be 1, 2 or 8 (vectors), got %ld", value);
+        G.shift_overlap = value;
+    }
     else if (!strcmp(key, "slot_timing")) G.slot_timing = value;
     else if (!strcmp(key, "spin_slack_ns")) G.spin_slack_ns = std::max(0L, value);
     else if (!strcmp(key, "lanes")) G.lanes = value >= 2 ? 2 : 1;
@@ -701,6 +706,7 @@ extern "C" long dlnb_get(const char *key) {
     if (!strcmp(key, "spin_regs")) return G.spin_regs;
     if (!strcmp(key, "strict_barriers")) return G.strict_barriers;
     if (!strcmp(key, "align_iterations")) return G.align_iterations;
+    if (!strcmp(key, "shift_overlap")) return G.shift_overlap;
     // 1 when a CTA of the emulated compute and a 512-thread collective CTA (96 registers) fit on one SM together
     if (!strcmp(key, "spin_coresident")) {
         const long per_sm = ((G.spin_ctas > 0 ? G.spin_ctas : G.sms) + G.sms - 1) / G.sms;
@@ -938,6 +944,8 @@ static int pick_grid(long want, long want_mc, int dtype, int op, int n, int thre
         // the switch does the adding / replicating: few CTAs saturate the links. Measured (profiles/):
         // 16 CTAs best on 8 GPUs (more is slower), 32 on 4 (16 leaves a quarter of the rate unused)
         g = want_mc > 0 ? want_mc : (n >= 8 ? 16 : 32);
+    } else if (op == OP_AR2 && n == 2) {
+        g = 64; // measured on 2 GPUs (profiles/r02): 632 / 666 / 676 GB/s at 64 MiB / 256 MiB / 1 GiB with 64 CTAs, 587 / 653 / 671 with 128
     } else {
         g = 128; // NVLink-bound peer loads/stores: measured best for >= 64 MB, harmless below
     }
@@ -1082,6 +1090,7 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
         v.mc_send = is_switch_op(op) ? mc_s : nullptr;
         v.mc_recv = is_switch_op(op) ? mc_r : nullptr;
         v.strict = (int)G.strict_barriers;
+        v.shift_overlap = (int)G.shift_overlap;
         v.ctl = G.ctl + (c->id * 2 + lane);
         v.host_error = G.host_error_dev;
         v.timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;
@@ -1702,6 +1711,7 @@ static int emu(int op, int nranks, const void *const *send, void *const *recv, s
         v.host_error = G.host_error_dev;
         v.timeout_ns = 10ull * 1000000000ull;
         v.strict = (int)G.strict_barriers;
+        v.shift_overlap = (int)G.shift_overlap;
     }
     const int threads = 512;
     int occ = occupancy_dtype(dtype, op, nranks, threads);
@@ -1840,6 +1850,7 @@ extern "C" int dlnb_emu_allreduce_noalloc(int nranks, const void *const *send, v
         v.ctl = (CommCtl *)(scratch + DLNB_NOALLOC_FLAG_BYTES + (size_t)r * DLNB_NOALLOC_MAX_CTAS * 4);
         v.host_error = G.host_error_dev;
         v.timeout_ns = 10ull * 1000000000ull;
+        v.shift_overlap = (int)G.shift_overlap;
     }
     const int threads = 512;
     const int occ = occupancy_dtype(dtype, op, nranks, threads);

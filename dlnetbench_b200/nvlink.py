@@ -11,34 +11,71 @@ import time
 
 
 class LinkCounters:
+    """Tries, in order: NVML field values summed by the driver (scope UINT_MAX), the same fields per link (scope =
+    link 0..17) summed here, and `nvidia-smi nvlink -gt d` (the tool's own reading of the data counters)."""
+
     def __init__(self, device_index: int):
-        self.ok, self.why = False, ""
-        try:
-            import pynvml as nv
+        self.ok, self.why, self.how, self.index = False, "", "", device_index
+        errs = []
+        for how in ("nvml_sum", "nvml_per_link", "nvidia_smi"):
+            try:
+                self.how = how
+                if how != "nvidia_smi":
+                    import pynvml as nv
 
-            nv.nvmlInit()
-            self.nv = nv
-            self.h = nv.nvmlDeviceGetHandleByIndex(device_index)
-            self.fields = [("data_tx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX), ("data_rx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX),
-                           ("raw_tx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_TX), ("raw_rx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_RX)]
-            self.read()
-            self.ok = True
-        except Exception as e:  # no NVML, no NVLink, or counters not exposed on this box
-            self.why = f"{type(e).__name__}: {e}"
+                    nv.nvmlInit()
+                    self.nv = nv
+                    self.h = nv.nvmlDeviceGetHandleByIndex(device_index)
+                    self.fields = [("data_tx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX), ("data_rx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX),
+                                   ("raw_tx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_TX), ("raw_rx", nv.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_RX)]
+                first = self.read()
+                if not any(first.values()) and how != "nvidia_smi":
+                    raise RuntimeError("all counters read zero")
+                self.ok = True
+                return
+            except Exception as e:  # no NVML, no NVLink, or counters not exposed this way on this box
+                errs.append(f"{how}: {type(e).__name__}: {e}")
+        self.why = "; ".join(errs)
 
-    def read(self) -> dict:
-        """Counters in bytes (scope UINT_MAX = sum over all links of the GPU)."""
+    def _fields(self, scope) -> dict:
         nv = self.nv
-        vals = nv.nvmlDeviceGetFieldValues(self.h, [(fid, 0xFFFFFFFF) for _, fid in self.fields])
+        vals = nv.nvmlDeviceGetFieldValues(self.h, [(fid, scope) for _, fid in self.fields])
         out = {}
         for (name, _), v in zip(self.fields, vals):
             if v.nvmlReturn != nv.NVML_SUCCESS:
-                raise RuntimeError(f"NVML field {name}: return code {v.nvmlReturn}")
+                raise RuntimeError(f"NVML field {name} scope {scope}: return code {v.nvmlReturn}")
             t = v.valueType
             val = (v.value.ullVal if t == nv.NVML_VALUE_TYPE_UNSIGNED_LONG_LONG else v.value.ulVal if t == nv.NVML_VALUE_TYPE_UNSIGNED_LONG
                    else v.value.uiVal if t == nv.NVML_VALUE_TYPE_UNSIGNED_INT else int(v.value.dVal))
             out[name] = int(val) * 1024
         return out
+
+    def read(self) -> dict:
+        """Counters in bytes, summed over the links of the GPU."""
+        if self.how == "nvml_sum":
+            return self._fields(0xFFFFFFFF)
+        if self.how == "nvml_per_link":
+            tot, seen = {}, 0
+            for link in range(18):
+                try:
+                    one = self._fields(link)
+                except RuntimeError:
+                    continue
+                seen += 1
+                for k, v in one.items():
+                    tot[k] = tot.get(k, 0) + v
+            if not seen:
+                raise RuntimeError("no link answered")
+            return tot
+        import re
+        import subprocess
+
+        txt = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(self.index)], capture_output=True, text=True, timeout=20).stdout
+        tx = sum(int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", txt))
+        rx = sum(int(x) for x in re.findall(r"Data Rx:\s*(\d+)\s*KiB", txt))
+        if not re.search(r"Data Tx", txt):
+            raise RuntimeError("nvidia-smi nvlink -gt d printed no counters: " + txt[:120].replace("\n", " "))
+        return {"data_tx": tx * 1024, "data_rx": rx * 1024}
 
     def settle(self) -> dict:
         """Read after the counters had time to catch up with finished work."""

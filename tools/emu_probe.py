@@ -40,14 +40,18 @@ def main() -> None:
     ap.add_argument("--ops", nargs="+", default=["allreduce", "allgather", "reduce_scatter", "alltoall"])
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--ctas", type=int, default=0, help="CTAs per virtual rank (0 = as many as stay co-resident)")
+    ap.add_argument("--odd", action="store_true", help="odd shard / block counts: rank r's chunk starts at r*count*2 bytes, the misaligned (shifted) mover runs")
+    ap.add_argument("--shift-overlap", type=int, default=0, help="window overlap of the shifted mover in vectors (1, 2 or 8; 0 = library default)")
     args = ap.parse_args()
 
     capi.init(0, 1)
+    if args.shift_overlap:
+        capi.set_option("shift_overlap", args.shift_overlap)
     dtype, esz = capi.F16, 2
     total = int(args.mib * (1 << 20)) // esz          # elements of the large buffer of one rank
     rows = []
     for n in args.nranks:
-        unit = total // n // 8 * 8                      # per-peer block / shard, 16-byte aligned
+        unit = total // n // 8 * 8 + (1 if args.odd else 0)  # per-peer block / shard, 16-byte aligned unless --odd
         big = [capi.Tensor(unit * n, dtype) for _ in range(n)]
         big2 = [capi.Tensor(unit * n, dtype) for _ in range(n)]
         for r, t in enumerate(big):
@@ -72,7 +76,7 @@ def main() -> None:
                 call()
                 best = min(best, time.perf_counter() - t0)
             tb = traffic_bytes(op, n, s_bytes)
-            rows.append({"op": op, "virtual_ranks": n, "bytes_per_rank_unit": s_bytes, "us": round(best * 1e6, 1),
+            rows.append({"op": op, "virtual_ranks": n, "odd": args.odd, "shift_overlap": capi.get_option("shift_overlap"), "bytes_per_rank_unit": s_bytes, "us": round(best * 1e6, 1),
                          "hbm_traffic_bytes": tb, "hbm_GBps": round(tb / best / 1e9, 1)})
             print(json.dumps(rows[-1]), flush=True)
         for t in big + big2:
