@@ -407,17 +407,23 @@ def main():
                                   "hbm_1cta_per_sm": (0, 256, "hbm"), "fma_1024thr_per_sm_no_room": (0, 1024, "fma")}.items():
             set_footprint(c, th, m)
             barrier()
-            capi.compute_spin(a.buckets * kern_avg_ms * 1000 * 6 + 20000)  # compute that outlasts the batch, NOT waited for
+            spin_us = a.buckets * kern_avg_ms * 1000 * 6 + 20000
+            t_spin = time.perf_counter()
+            capi.compute_spin(spin_us)  # compute that outlasts the batch, NOT waited for
             capi.set_option("slot_timing", 0)
             capi.batch_begin_concurrent(a.buckets * 25.0)
             for i in range(a.buckets):
                 comm.Iallreduce(grad[i].data, summed[i].data, sizes[i], i)
             comm.WaitAll(a.buckets)
-            ms = max_over_ranks(capi.batch_end() / a.buckets)
+            ms_local = capi.batch_end() / a.buckets
+            t_batch = (time.perf_counter() - t_spin) * 1e3  # (before any torch collective: NCCL's own kernel would queue for SMs too)
             capi.set_option("slot_timing", 1)
-            contention[name] = {"avg_launch_ms": ms, "slowdown": ms / kern_avg_ms, "coresident": capi.get_option("spin_coresident"),
-                                "spin_ctas": capi.get_option("spin_ctas"), "spin_threads": th, "sms": sms}
             capi.compute_sync()
+            ms = max_over_ranks(ms_local)
+            contention[name] = {"avg_launch_ms": ms, "slowdown": ms / kern_avg_ms, "coresident": capi.get_option("spin_coresident"),
+                                "spin_ctas": capi.get_option("spin_ctas"), "spin_threads": th, "sms": sms,
+                                "spin_ms": spin_us / 1e3, "batch_done_after_ms": max_over_ranks(t_batch),
+                                "ran_beside_the_compute": bool(max_over_ranks(t_batch) < 0.8 * spin_us / 1e3)}
         set_footprint(a.spin_ctas, a.spin_threads, a.spin_mode)
 
     # ---- end to end: host buffers in, host result out, copies inside the timed region

@@ -273,6 +273,10 @@ __device__ __forceinline__ void reduce_store_vec(const uint4 *const *src, uint4 
                 for (int p = 0; p < NSRC; ++p) val[u][p] = RO ? ld_v4_ro(s[p] + i) : ld_v4(s[p] + i);
             }
         }
+        // Programmatic dependent launch (world-1 copies only, see coll_kernel): once this CTA's LAST tile is
+        // loaded, the next kernel of the stream may start filling the machine while this one drains. A no-op
+        // for kernels that were not launched with the attribute.
+        if (RO && (t + nctas) * tile >= nvec) asm volatile("griddepcontrol.launch_dependents;");
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const size_t i = base + (size_t)u * bdim;
@@ -787,6 +791,12 @@ __device__ __forceinline__ void run_op(const RankView &v, size_t count, int cta,
 template <typename T, int NR, int OP>
 __global__ void __maxnreg__(DLNB_COLL_REGS(NR))
 coll_kernel(const __grid_constant__ RankView v, size_t count) {
+    // World 1: consecutive collectives of a stream are launched with programmatic stream serialization, so this
+    // kernel may be resident before its predecessor has finished. Nothing is read or written before the
+    // predecessor's memory operations are complete and visible (a later collective may read what an earlier one
+    // wrote, e.g. fsdp's gather buffer). Groups > 1 are never launched that way: a kernel that waits on its
+    // peers must not hold SMs its predecessor's peers are waiting for.
+    if (NR == 1) asm volatile("griddepcontrol.wait;" ::: "memory");
     run_op<T, NR, OP>(v, count, blockIdx.x, gridDim.x);
 }
 

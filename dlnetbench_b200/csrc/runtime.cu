@@ -207,7 +207,7 @@ struct State {
     int next_comm = 0;
     std::vector<int> free_comm_ids; // ids of destroyed communicators (same order on every rank), reused after a reset
     std::vector<dlnb_comm *> comms;
-    long strict_barriers = 0, align_iterations = 1, shift_overlap = 8;
+    long strict_barriers = 0, align_iterations = 1, shift_overlap = 8, pdl = 1;
     // point-to-point mailboxes (symmetric, one per peer world rank) and sequence state (local)
     P2PBox *p2p_boxes = nullptr;
     P2PState *p2p_state = nullptr;
@@ -561,6 +561,7 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     if (const char *v = getenv("DLNB_SPIN_THREADS")) G.spin_threads = std::min(1024L, std::max(32L, atol(v)));
     if (const char *v = getenv("DLNB_STRICT_BARRIERS")) G.strict_barriers = atol(v) != 0;
     if (const char *v = getenv("DLNB_ALIGN")) G.align_iterations = atol(v) != 0;
+    if (const char *v = getenv("DLNB_PDL")) G.pdl = atol(v) != 0;
     if (const char *v = getenv("DLNB_SHIFT_OVERLAP")) { const long o = atol(v); if (o == 1 || o == 2 || o == 8) G.shift_overlap = o; }
 
     G.inited = true;
@@ -687,6 +688,7 @@ extern "C" int dlnb_set(const char *key, long value) {
         G.spin_smem = value;
     } else if (!strcmp(key, "strict_barriers")) G.strict_barriers = value != 0;
     else if (!strcmp(key, "align_iterations")) G.align_iterations = value != 0;
+    else if (!strcmp(key, "pdl")) G.pdl = value != 0;
     else if (!strcmp(key, "shift_overlap")) {
         if (value != 1 && value != 2 && value != 8) return fail("dlnb_set: shift_overlap must be 1, 2 or 8 (vectors), got %ld", value);
         G.shift_overlap = value;
@@ -707,6 +709,7 @@ extern "C" long dlnb_get(const char *key) {
     if (!strcmp(key, "strict_barriers")) return G.strict_barriers;
     if (!strcmp(key, "align_iterations")) return G.align_iterations;
     if (!strcmp(key, "shift_overlap")) return G.shift_overlap;
+    if (!strcmp(key, "pdl")) return G.pdl;
     // 1 when a CTA of the emulated compute and a 512-thread collective CTA (96 registers) fit on one SM together
     if (!strcmp(key, "spin_coresident")) {
         const long per_sm = ((G.spin_ctas > 0 ? G.spin_ctas : G.sms) + G.sms - 1) / G.sms;
@@ -896,11 +899,11 @@ extern "C" int dlnb_spin_calibrate(double *overhead_us, double *slope) {
 // collective launch
 // ---------------------------------------------------------------------------
 static cudaError_t launch_dtype(int dtype, int op, int nr, dim3 grid, int threads, cudaStream_t s,
-                                const EmuViews &ev, size_t count, bool coop) {
+                                const EmuViews &ev, size_t count, bool coop, bool pdl = false) {
     switch (dtype) {
-    case DLNB_F32: return launch_coll_f32(op, nr, grid, threads, s, ev, count, coop);
-    case DLNB_F16: return launch_coll_f16(op, nr, grid, threads, s, ev, count, coop);
-    case DLNB_BF16: return launch_coll_bf16(op, nr, grid, threads, s, ev, count, coop);
+    case DLNB_F32: return launch_coll_f32(op, nr, grid, threads, s, ev, count, coop, pdl);
+    case DLNB_F16: return launch_coll_f16(op, nr, grid, threads, s, ev, count, coop, pdl);
+    case DLNB_BF16: return launch_coll_bf16(op, nr, grid, threads, s, ev, count, coop, pdl);
     }
     return cudaErrorInvalidValue;
 }
@@ -1094,7 +1097,7 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
         v.ctl = G.ctl + (c->id * 2 + lane);
         v.host_error = G.host_error_dev;
         v.timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;
-        cudaError_t e = launch_dtype(c->dtype, op, c->n, dim3(grid, 1, 1), threads, st, ev, count, false);
+        cudaError_t e = launch_dtype(c->dtype, op, c->n, dim3(grid, 1, 1), threads, st, ev, count, false, c->n == 1 && G.pdl && !G.capturing);
         if (e != cudaSuccess) return fail("collective launch failed: %s", cudaGetErrorString(e));
         G.launches++;
     }

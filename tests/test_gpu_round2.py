@@ -317,3 +317,45 @@ def test_fsdp_binary_graph_and_plain_agree(dl):
     assert rs_ms > 0.03, rs_ms
     assert graph >= lb_ms + 0.8 * 8 * rs_ms, (graph, lb_ms, rs_ms)
     assert abs(graph - plain) <= 0.12 * plain, (graph, plain)
+
+
+@pytest.mark.parametrize("n", [2, 5, 8])
+def test_kernels_write_only_inside_their_buffers(dl, oracle, n):
+    """compute-sanitizer is closed on this pool, so the bounds check is ours: every receive buffer is a window inside one
+    big allocation whose every other byte holds a canary pattern; after each collective (odd counts, odd element offsets:
+    head / tail peeling, aligned and shifted 128-bit movers, several CTAs) the canaries around the windows are intact and
+    the windows hold the oracle's result."""
+    dtype, guard = 1, 4099
+    for count, off in ((1, 1), (33, 3), (4097, 5), (300_001, 7)):
+        span = count * n + 2 * guard + 16
+        arena = [dl.Tensor(span, dtype) for _ in range(n)]      # receive side: canary everywhere, window in the middle
+        for r, t in enumerate(arena):
+            t.fill(2, 999, r)
+        lo = guard + off                                          # window [lo, lo + len) in elements
+        xs = [oracle.fill_pattern(count * n, dtype, 2, 31, r) for r in range(n)]
+        send = make_dev(dl, xs, dtype)
+
+        def canaries_intact(length):
+            for r, t in enumerate(arena):
+                assert dl.verify_sum_pattern(t.data, lo, 0, dtype, 2, 999, [r]) == 0, ("below the window", n, count, r)
+                hi = lo + length
+                assert dl.verify_sum_pattern(t.offset(hi), span - hi, hi, dtype, 2, 999, [r]) == 0, ("above the window", n, count, r)
+
+        # allreduce (both algorithms) into a window of `count`
+        want = oracle.allreduce([x[:count] for x in xs], dtype)
+        for algo in (1, 2):
+            dl.emu_allreduce([t.data for t in send], [t.offset(lo) for t in arena], count, dtype, algo=algo, ctas=3)
+            canaries_intact(count)
+            got = arena[n - 1].download(np.float16)[lo:lo + count]
+            assert np.array_equal(bits(got), bits(want)), (n, count, algo)
+        # reduce-scatter into a window of `count`
+        dl.emu_reduce_scatter([t.data for t in send], [t.offset(lo) for t in arena], count, dtype, ctas=3)
+        canaries_intact(count)
+        # allgather / all-to-all into a window of n * count
+        dl.emu_allgather([t.data for t in send], [t.offset(lo) for t in arena], count, dtype, ctas=3)
+        canaries_intact(count * n)
+        dl.emu_alltoall([t.data for t in send], [t.offset(lo) for t in arena], count, dtype, ctas=3)
+        canaries_intact(count * n)
+        got = arena[0].download(np.float16)[lo:lo + count * n]
+        assert np.array_equal(bits(got), bits(oracle.alltoall(xs, 0, count, dtype)))
+        free_all(arena, send)

@@ -10,6 +10,7 @@
 //
 // build: nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o bin/peer_copy_peak tools/peer_copy_peak.cu
 #include <cuda_runtime.h>
+#include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -36,6 +37,44 @@ __global__ void __launch_bounds__(512) copy_kernel(const uint4 *__restrict__ src
         dst[i + 3 * stride] = d;
     }
     for (; i < nvec; i += stride) dst[i] = src[i];
+}
+
+// bulk-async staged copy: one thread per CTA drives a ring of STAGES chunks, cp.async.bulk global -> smem (mbarrier
+// complete_tx) and smem -> global (bulk_group); either side may be peer memory. Same code as tools/explore/bulk_copybench.cu.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_wait(uint64_t *b, unsigned parity) {
+    asm volatile("{\n.reg .pred p;\nW:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra D;\nbra W;\nD:\n}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem, const void *g, unsigned bytes, uint64_t *b) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem)), "l"(g), "r"(bytes),
+                 "r"(smem_u32(b)) : "memory");
+}
+template <int STAGES>
+__global__ void __launch_bounds__(32) bulk_copy(const char *__restrict__ src, char *__restrict__ dst, size_t bytes, unsigned chunk) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t *bar = (uint64_t *)smem;
+    unsigned char *stage = smem + 128;
+    if (threadIdx.x != 0) return;
+    for (int s = 0; s < STAGES; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar + s)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const size_t nchunks = (bytes + chunk - 1) / chunk;
+    const size_t mine = nchunks > blockIdx.x ? (nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    auto off = [&](size_t k) { return (blockIdx.x + k * gridDim.x) * (size_t)chunk; };
+    auto len = [&](size_t k) { size_t o = off(k); return (unsigned)(bytes - o < chunk ? bytes - o : chunk); };
+    for (size_t k = 0; k < mine && k < STAGES; ++k) bulk_g2s(stage + k * chunk, src + off(k), len(k), bar + k);
+    for (size_t k = 0; k < mine; ++k) {
+        const int s = (int)(k % STAGES);
+        mbar_wait(bar + s, (unsigned)((k / STAGES) & 1));
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + off(k)), "r"(smem_u32(stage + (size_t)s * chunk)), "r"(len(k)) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (k >= 1 && k - 1 + STAGES < mine) {
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            const size_t r = k - 1 + STAGES;
+            bulk_g2s(stage + (size_t)(r % STAGES) * chunk, src + off(r), len(r), bar + (r % STAGES));
+        }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 struct Dev {
@@ -88,7 +127,14 @@ int main(int argc, char **argv) {
     }
     const size_t nvec = bytes / 16;
 
-    // mode: 0 copy engine, 1 kernel push (runs on the source), 2 kernel pull (runs on the destination)
+    const unsigned chunk = 32768;
+    const size_t bulk_smem = 128 + 4 * (size_t)chunk;
+    for (int i = 0; i < n; ++i) {
+        CK(cudaSetDevice(i));
+        CK(cudaFuncSetAttribute(bulk_copy<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bulk_smem));
+    }
+    // mode: 0 copy engine, 1 kernel push (runs on the source), 2 kernel pull (runs on the destination),
+    //       3 / 4 the same two with the bulk-async staged copy (32 KiB chunks, 4 stages, one CTA per SM)
     // pairs: list of (src, dst) transfers active at once; the time is the slowest stream's
     auto run = [&](const char *name, int mode, const std::vector<std::pair<int, int>> &pairs) {
         double best = 1e30;
@@ -96,12 +142,13 @@ int main(int argc, char **argv) {
             for (int i = 0; i < n; ++i) { CK(cudaSetDevice(i)); CK(cudaDeviceSynchronize()); }
             std::vector<int> used;
             for (auto &p : pairs) {
-                const int runner = mode == 2 ? p.second : p.first;
+                const int runner = (mode == 2 || mode == 4) ? p.second : p.first;
                 CK(cudaSetDevice(runner));
                 bool first = true;
                 for (int u : used) first = first && u != runner;
                 if (first) { CK(cudaEventRecord(d[runner].e0, d[runner].s)); used.push_back(runner); }
                 if (mode == 0) CK(cudaMemcpyPeerAsync(d[p.second].b, p.second, d[p.first].a, p.first, bytes, d[runner].s));
+                else if (mode >= 3) bulk_copy<4><<<148, 32, bulk_smem, d[runner].s>>>(d[p.first].a, d[p.second].b, bytes, chunk);
                 else copy_kernel<<<ctas, 512, 0, d[runner].s>>>((const uint4 *)d[p.first].a, (uint4 *)d[p.second].b, nvec);
             }
             double worst = 0;
@@ -133,6 +180,10 @@ int main(int argc, char **argv) {
     run("kernel_push_both_directions", 1, {{0, 1}, {1, 0}});
     run("kernel_pull_one_direction", 2, {{0, 1}});
     run("kernel_pull_both_directions", 2, {{0, 1}, {1, 0}});
+    run("bulk_async_push_one_direction", 3, {{0, 1}});
+    run("bulk_async_push_both_directions", 3, {{0, 1}, {1, 0}});
+    run("bulk_async_pull_one_direction", 4, {{0, 1}});
+    run("bulk_async_pull_both_directions", 4, {{0, 1}, {1, 0}});
     if (n > 2) {
         std::vector<std::pair<int, int>> all;
         for (int k = 1; k < n; ++k)

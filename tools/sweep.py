@@ -106,6 +106,7 @@ def main():
             for i in range(a.iters):
                 issue(send[i % nbuf], recv[i % nbuf], sc, rc, i)
             b2b = capi.iter_end() / a.iters
+            comm.WaitAll(a.iters)  # posted receives count as outstanding until they have been waited for
             wire = None
             if links:
                 from dlnetbench_b200 import nvlink
