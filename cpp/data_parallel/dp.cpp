@@ -90,7 +90,7 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
 
     std::vector<int> everyone((size_t)w.size);
     for (int r = 0; r < w.size; r++) everyone[r] = r;
-    B200Communicator *communicator = new B200Communicator(everyone, num_buckets, ProxyDtype<T>::value);
+    ProxyBackend *communicator = new ProxyBackend(everyone, num_buckets, ProxyDtype<T>::value);
     communicator->set("algo", b200::algo_from_name(cli.algo));
     if (cli.ctas > 0) communicator->set("ctas", cli.ctas);
 

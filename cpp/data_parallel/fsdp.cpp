@@ -46,7 +46,7 @@ void run_fsdp(Tensor<T, device> **shard_params, Tensor<T, device> *layer_params,
     timer_allgather.start();
     unit_comm->Allgather(shard_params[0]->data, shard_count(0), layer_params->data, shard_count(0));
     timer_allgather.stop();
-    if (!in_graph_capture) first_allgather_ms = static_cast<B200Communicator *>(unit_comm)->slot_ms(-1);
+    if (!in_graph_capture) first_allgather_ms = static_cast<ProxyBackend *>(unit_comm)->slot_ms(-1);
 
     // forward: gather unit u+1 while unit u computes (the last unit's forward is not emulated,
     // as in the reference: U-1 sleeps)
@@ -154,8 +154,8 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
     std::vector<int> unit_group, replica_group;
     for (unsigned i = 0; i < sharding_factor; i++) unit_group.push_back((int)((unsigned)w.rank / sharding_factor * sharding_factor + i));
     for (unsigned i = 0; i < num_replicas; i++) replica_group.push_back((int)((unsigned)w.rank % sharding_factor + i * sharding_factor));
-    B200Communicator *unit_comm_proxy = new B200Communicator(unit_group, (int)num_units, ProxyDtype<T>::value);
-    B200Communicator *allreduce_comm_proxy = new B200Communicator(replica_group, (int)num_units, ProxyDtype<T>::value);
+    ProxyBackend *unit_comm_proxy = new ProxyBackend(unit_group, (int)num_units, ProxyDtype<T>::value);
+    ProxyBackend *allreduce_comm_proxy = new ProxyBackend(replica_group, (int)num_units, ProxyDtype<T>::value);
     unit_comm_proxy->set("algo", b200::algo_from_name(cli.algo));
     allreduce_comm_proxy->set("algo", b200::algo_from_name(cli.algo));
     if (cli.ctas > 0) {

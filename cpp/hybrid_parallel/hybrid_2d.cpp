@@ -117,8 +117,8 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
     std::vector<int> dp_group, pp_group;
     for (int i = 0; i < dp_size; i++) dp_group.push_back(stage_id + i * num_stage);
     for (int i = 0; i < num_stage; i++) pp_group.push_back(w.rank / num_stage * num_stage + i);
-    B200Communicator *dp_communicator = new B200Communicator(dp_group, 1, ProxyDtype<T>::value);
-    B200Communicator *pp_communicator = new B200Communicator(pp_group, 1, ProxyDtype<T>::value);
+    ProxyBackend *dp_communicator = new ProxyBackend(dp_group, 1, ProxyDtype<T>::value);
+    ProxyBackend *pp_communicator = new ProxyBackend(pp_group, 1, ProxyDtype<T>::value);
     dp_communicator->set("algo", b200::algo_from_name(cli.algo));
     if (cli.ctas > 0) {
         dp_communicator->set("ctas", cli.ctas);

@@ -153,9 +153,9 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
     for (int i = 0; i < E; i++) ep_group.push_back((dp_id * S + stage_id) * E + i);
     for (int i = 0; i < S; i++) pp_group.push_back((dp_id * S + i) * E + ep_id);
     for (int i = 0; i < dp_size; i++) dp_group.push_back((i * S + stage_id) * E + ep_id);
-    B200Communicator *dp_communicator = new B200Communicator(dp_group, 1, ProxyDtype<T>::value);
-    B200Communicator *pp_communicator = new B200Communicator(pp_group, 1, ProxyDtype<T>::value);
-    B200Communicator *ep_communicator_ = new B200Communicator(ep_group, 1, ProxyDtype<T>::value);
+    ProxyBackend *dp_communicator = new ProxyBackend(dp_group, 1, ProxyDtype<T>::value);
+    ProxyBackend *pp_communicator = new ProxyBackend(pp_group, 1, ProxyDtype<T>::value);
+    ProxyBackend *ep_communicator_ = new ProxyBackend(ep_group, 1, ProxyDtype<T>::value);
     dp_communicator->set("algo", b200::algo_from_name(cli.algo));
     ep_communicator_->set("algo", b200::algo_from_name(cli.algo));
     if (cli.ctas > 0) {

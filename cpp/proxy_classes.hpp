@@ -106,13 +106,13 @@ class B200Communicator : public ProxyCommunicator {
     // 64-bit element counts (the C ABI takes size_t). The interface above counts in int, and the
     // reference narrows its uint64_t sizes into it (dp.cpp:99, hybrid_2d.cpp:162, hybrid_3d_moe.cpp:207),
     // which wraps beyond 2^31-1 elements — e.g. the per-stage gradients of mixtral_8x7b on one box.
-    void Allreduce64(const void *sendbuf, void *recvbuf, uint64_t count) {
+    virtual void Allreduce64(const void *sendbuf, void *recvbuf, uint64_t count) {
         B200_CHECK(dlnb_allreduce(comm, sendbuf, recvbuf, (size_t)count));
     }
-    void Iallreduce64(const void *sendbuf, void *recvbuf, uint64_t count, int index) {
+    virtual void Iallreduce64(const void *sendbuf, void *recvbuf, uint64_t count, int index) {
         B200_CHECK(dlnb_iallreduce(comm, sendbuf, recvbuf, (size_t)count, index));
     }
-    void set(const char *key, long v) { B200_CHECK(dlnb_comm_set(comm, key, v)); }
+    virtual void set(const char *key, long v) { B200_CHECK(dlnb_comm_set(comm, key, v)); }
     float slot_ms(int index) {
         float ms = 0;
         B200_CHECK(dlnb_slot_elapsed(comm, index, &ms));
@@ -121,7 +121,7 @@ class B200Communicator : public ProxyCommunicator {
     dlnb_comm_t handle() const { return comm; }
     int size() const { return comm_size; }
 
-  private:
+  protected:
     static size_t elems(int count) {
         if (count < 0) {
             // the reference narrows uint64_t sizes to int (dp.cpp:99, fsdp.cpp:88): diagnose the wrap
@@ -141,6 +141,104 @@ class B200Communicator : public ProxyCommunicator {
     int comm_size = 1;
     int rank = 0;
 };
+
+#ifdef PROXY_ENABLE_NCCL
+// ------------------------------------------------------------------------------------------------
+// COMPARISON backend, `nccl` build only (Makefile.flags.mk): what the reference's CCLCommunicator does
+// (cpp/proxy_classes.hpp:135-253) — every collective one NCCL call — inside the same proxies, beside the
+// same emulated compute, on the same buffers and with the same slot / timing bookkeeping as the product
+// (dlnb_foreign_begin / dlnb_foreign_end put the NCCL call on libdlnb's communication stream, ordered
+// after the compute enqueued so far). Never part of the `b200` build; there is no run-time switch.
+// ------------------------------------------------------------------------------------------------
+#include <nccl.h>
+
+#define NCCL_CHECK(call)                                                                          \
+    do {                                                                                          \
+        ncclResult_t r_ = (call);                                                                 \
+        if (r_ != ncclSuccess) {                                                                  \
+            fprintf(stderr, "[rank %d] %s failed: %s\n", dlnb_rank(), #call, ncclGetErrorString(r_)); \
+            fflush(stderr);                                                                       \
+            _exit(1);                                                                             \
+        }                                                                                         \
+    } while (0)
+
+class CCLCommunicator : public B200Communicator {
+  public:
+    CCLCommunicator(const std::vector<int> &group, int num_slots, int dtype) : B200Communicator(group, num_slots, dtype) {
+        nccl_dtype = dtype == DLNB_F32 ? ncclFloat : dtype == DLNB_F16 ? ncclHalf : ncclBfloat16;
+        // one ncclUniqueId per group: every rank offers one, the group uses its first member's
+        // (the reference broadcasts rank 0's over MPI, dp.cpp:181-186)
+        ncclUniqueId mine;
+        NCCL_CHECK(ncclGetUniqueId(&mine));
+        std::vector<ncclUniqueId> all((size_t)dlnb_world());
+        B200_CHECK(dlnb_host_allgather(&mine, sizeof(mine), all.data()));
+        NCCL_CHECK(ncclCommInitRank(&nccl, (int)group.size(), all[(size_t)group[0]], dlnb_comm_rank(handle())));
+    }
+    std::string get_name() override { return "NCCL"; }
+    void set(const char *, long) override {} // kernel knobs of the product do not apply
+
+    void Iallreduce(const void *s, void *r, int count, int index) override { Iallreduce64(s, r, (uint64_t)elems(count), index); }
+    void Allreduce(const void *s, void *r, int count) override { Allreduce64(s, r, (uint64_t)elems(count)); }
+    void Iallreduce64(const void *s, void *r, uint64_t count, int index) override {
+        run(index, [&](cudaStream_t st) { NCCL_CHECK(ncclAllReduce(s, r, (size_t)count, nccl_dtype, ncclSum, nccl, st)); });
+    }
+    void Allreduce64(const void *s, void *r, uint64_t count) override {
+        Iallreduce64(s, r, count, -1);
+        Wait(-1);
+    }
+    void Iallgather(const void *s, int sendcount, void *r, int recvcount, int index) override {
+        same(sendcount, recvcount);
+        run(index, [&](cudaStream_t st) { NCCL_CHECK(ncclAllGather(s, r, elems(sendcount), nccl_dtype, nccl, st)); });
+    }
+    void Allgather(const void *s, int sendcount, void *r, int recvcount) override {
+        Iallgather(s, sendcount, r, recvcount, -1);
+        Wait(-1);
+    }
+    void Reduce_Scatter_block(const void *s, void *r, int recvcount) override {
+        run(-1, [&](cudaStream_t st) { NCCL_CHECK(ncclReduceScatter(s, r, elems(recvcount), nccl_dtype, ncclSum, nccl, st)); });
+        Wait(-1);
+    }
+    void Alltoall(const void *s, int sendcount, void *r, int recvcount) override { // grouped send/recv, as the reference :160-182
+        same(sendcount, recvcount);
+        const size_t bytes = elems(sendcount) * (nccl_dtype == ncclFloat ? 4 : 2);
+        run(-1, [&](cudaStream_t st) {
+            NCCL_CHECK(ncclGroupStart());
+            for (int p = 0; p < size(); ++p) {
+                NCCL_CHECK(ncclSend((const char *)s + (size_t)p * bytes, elems(sendcount), nccl_dtype, p, nccl, st));
+                NCCL_CHECK(ncclRecv((char *)r + (size_t)p * bytes, elems(recvcount), nccl_dtype, p, nccl, st));
+            }
+            NCCL_CHECK(ncclGroupEnd());
+        });
+        Wait(-1);
+    }
+    void send(const void *buf, int count, int dest) override { Isend(buf, count, dest, -1); Wait(-1); }
+    void recv(void *buf, int count, int source) override { Irecv(buf, count, source, -1); Wait(-1); }
+    void Isend(const void *buf, int count, int dest, int index) override {
+        run(index, [&](cudaStream_t st) { NCCL_CHECK(ncclSend(buf, elems(count), nccl_dtype, dest, nccl, st)); });
+    }
+    void Irecv(void *buf, int count, int source, int index) override {
+        run(index, [&](cudaStream_t st) { NCCL_CHECK(ncclRecv(buf, elems(count), nccl_dtype, source, nccl, st)); });
+    }
+    void finalize() override {
+        if (nccl) NCCL_CHECK(ncclCommDestroy(nccl)); // (the reference never gets here: `#ifdef PROXY_ENABLE_CLL`, dp.cpp:298)
+        nccl = nullptr;
+        B200Communicator::finalize();
+    }
+
+  private:
+    template <typename Fn> void run(int slot, Fn fn) {
+        void *st = nullptr;
+        B200_CHECK(dlnb_foreign_begin(handle(), slot, &st));
+        fn((cudaStream_t)st);
+        B200_CHECK(dlnb_foreign_end(handle(), slot));
+    }
+    ncclComm_t nccl = nullptr;
+    ncclDataType_t nccl_dtype = ncclFloat;
+};
+using ProxyBackend = CCLCommunicator;
+#else
+using ProxyBackend = B200Communicator;
+#endif
 
 // Allreduce of `count` elements through the interface when the count fits its int, through the
 // 64-bit entry of the B200 backend when it does not (another backend would wrap: refuse).

@@ -94,6 +94,8 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_launch_count": (u64, []),
         "dlnb_iter_begin": (i, []),
         "dlnb_iter_end": (i, [C.POINTER(C.c_float)]),
+        "dlnb_foreign_begin": (i, [vp, i, pvp]),
+        "dlnb_foreign_end": (i, [vp, i]),
         "dlnb_batch_begin": (i, []),
         "dlnb_batch_begin_concurrent": (i, [C.c_double]),
         "dlnb_batch_end": (i, [C.POINTER(C.c_float)]),

@@ -259,11 +259,17 @@ __device__ __forceinline__ void reduce_store_vec(const uint4 *const *src, uint4 
     for (int q = 0; q < NDST; ++q) d[q] = dst[q];
 
     // Tiled: a CTA streams contiguous tiles of U*blockDim.x vectors (tile index strides by the
-    // grid), a warp touches 512 contiguous bytes per load instruction.
+    // grid), a warp touches 512 contiguous bytes per load instruction. Tiles are laid out from the
+    // 128-byte line below the buffers of the side that crosses NVLink (the sources of a pull, the
+    // destinations of a push), so a warp's 512 bytes are 4 whole lines even when the buffer itself is
+    // only 16-byte aligned (bucket slices and shards rarely start on a line): `a0` vectors of the first
+    // tile lie before the data and are skipped (unsigned wrap makes i >= nvec for them).
     const size_t bdim = blockDim.x, tile = (size_t)U * bdim;
     const size_t cta = tid / bdim, nctas = nthr / bdim;
-    for (size_t t = cta; t * tile < nvec; t += nctas) {
-        const size_t base = t * tile + threadIdx.x;
+    const size_t a0 = (size_t)((((NSRC == 1) ? (uintptr_t)d[0] : (uintptr_t)s[0]) >> 4) & 7u);
+    const size_t nvirt = nvec + a0;
+    for (size_t t = cta; t * tile < nvirt; t += nctas) {
+        const size_t base = t * tile + threadIdx.x - a0;
         uint4 val[U][NSRC];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -276,7 +282,7 @@ __device__ __forceinline__ void reduce_store_vec(const uint4 *const *src, uint4 
         // Programmatic dependent launch (world-1 copies only, see coll_kernel): once this CTA's LAST tile is
         // loaded, the next kernel of the stream may start filling the machine while this one drains. A no-op
         // for kernels that were not launched with the attribute.
-        if (RO && (t + nctas) * tile >= nvec) asm volatile("griddepcontrol.launch_dependents;");
+        if (RO && (t + nctas) * tile >= nvirt) asm volatile("griddepcontrol.launch_dependents;");
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const size_t i = base + (size_t)u * bdim;
@@ -323,9 +329,10 @@ template <int NR> struct Unroll {
     // allgather: one local source, NR destinations (pointers, not data, fill the registers)
     static constexpr int U_AG = NR <= 4 ? 4 : 2;
     // shifted path: same loads in flight as the aligned path plus the shuffled neighbour
-    static constexpr int U_SH = NR == 1 ? 4 : NR == 2 ? 4 : 2;
+    static constexpr int U_SH = NR == 1 ? 4 : NR == 2 ? 4 : NR <= 6 ? 2 : 1;
     // ... of the bodies that also hold NR destination pointers (fused two-shot allreduce)
     static constexpr int U_SH_PUSH = NR <= 6 ? U_SH : 1;
+    static constexpr int U_PUSH = NR <= 6 ? U : 1; // 7-8 ranks: 8 loads in flight x 65,536 threads = 8 MB per GPU, three times the link's bandwidth-delay product
 };
 
 // ----------------------------------------------------------------------------
@@ -368,7 +375,9 @@ __device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src
     // (a 512-byte warp load then touches 4 lines, not 5) at the price of 2 / 8 vectors loaded twice per window.
     // Consecutive warps of a CTA take consecutive windows, CTAs stride by the grid.
     const long long run = 32 * U - (long long)overlap;
-    const long long a0 = overlap > 1 ? (long long)(((uintptr_t)s[0] >> 4) & (overlap - 1)) : 0;
+    // ... of the side that crosses NVLink: the sources of a pull, the destinations of a push (one local source)
+    const uintptr_t ref = NSRC == 1 ? (uintptr_t)d[0] : (uintptr_t)s[0];
+    const long long a0 = overlap > 1 ? (long long)((ref >> 4) & (overlap - 1)) : 0;
     const unsigned lane = threadIdx.x & 31u;
     const long long wpc = blockDim.x >> 5, warp = threadIdx.x >> 5;
     const long long cta = (long long)(tid / blockDim.x), nctas = (long long)(nthr / blockDim.x);
@@ -501,7 +510,7 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
     constexpr int PV = Elem<T>::PER_VEC;
     // slices in units of PV elements; the last rank also takes the sub-vector remainder
     const size_t nvec = count / PV;
-    const size_t per = (nvec + NR - 1) / NR;
+    const size_t per = ((nvec + NR - 1) / NR + 7) / 8 * 8; // slices of whole 128-byte lines
     const size_t e0 = min(per * (size_t)v.rank, nvec) * PV;
     const size_t e1 = v.rank == NR - 1 ? count : min(per * (size_t)(v.rank + 1), nvec) * PV;
     const T *src[NR];
@@ -511,7 +520,7 @@ __device__ __forceinline__ void allreduce_twoshot_body(const RankView &v, size_t
         src[p] = (const T *)v.send[p] + e0;
         dst[p] = (T *)v.recv[p] + e0;
     }
-    move_any<T, NR, NR, Unroll<NR>::U, Unroll<NR>::U_SH_PUSH>(src, dst, e1 - e0, cta, nctas, v.shift_overlap);
+    move_any<T, NR, NR, Unroll<NR>::U_PUSH, Unroll<NR>::U_SH_PUSH>(src, dst, e1 - e0, cta, nctas, v.shift_overlap);
 
     cta_barrier<true>(v, e + 2, cta); // publishes the pushed slices
     cta_finish(v, e + 2, cta);
@@ -636,7 +645,7 @@ __device__ __forceinline__ void allreduce_multimem_body(const RankView &v, size_
     constexpr int PV = Elem<T>::PER_VEC;
     constexpr int U = 8;
     const size_t nvec = count / PV;
-    const size_t per = (nvec + NR - 1) / NR;
+    const size_t per = ((nvec + NR - 1) / NR + 7) / 8 * 8; // slices of whole 128-byte lines
     const size_t v0 = min(per * (size_t)v.rank, nvec);
     const size_t n = min(v0 + per, nvec) - v0;
     const uint4 *src = (const uint4 *)v.mc_send + v0;

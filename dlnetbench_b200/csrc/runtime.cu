@@ -1118,6 +1118,36 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
     return 0;
 }
 
+// Hooks for work of ANOTHER library on the communication stream (the `nccl` comparison build, cpp/proxy_classes.hpp:
+// CCLCommunicator): the same ordering and slot bookkeeping a collective of this library gets — after the compute
+// enqueued so far, timed per slot, completion recorded for Wait / WaitAll — around a call the caller enqueues itself.
+extern "C" int dlnb_foreign_begin(dlnb_comm_t c, int slot, void **cuda_stream) {
+    NEED_INIT();
+    if (!c || !cuda_stream) return fail("null argument");
+    if (G.capturing) return fail("foreign work cannot be captured into a graph");
+    if (slot == -1) slot = c->num_slots;
+    else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range (communicator has %d)", slot, c->num_slots);
+    if (join_streams()) return 1;
+    if (drain_lane1_into_lane0()) return 1;
+    if (G.slot_timing) CU_TRY(cudaEventRecord(c->ev_start[slot], G.s_comm));
+    *cuda_stream = (void *)G.s_comm;
+    return 0;
+}
+extern "C" int dlnb_foreign_end(dlnb_comm_t c, int slot) {
+    NEED_INIT();
+    if (!c) return fail("null communicator");
+    if (slot == -1) slot = c->num_slots;
+    else if (slot < 0 || slot >= c->num_slots) return fail("slot %d out of range", slot);
+    if (mark_exclusive_on_lane0()) return 1;
+    if (G.slot_timing) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+    CU_TRY(cudaEventRecord(c->ev_done[slot], G.s_comm));
+    c->slot_timed[slot] = G.slot_timing ? 1 : 0;
+    c->slot_used[slot] = 1;
+    c->recv_src[slot] = -1;
+    G.launches++;
+    return 0;
+}
+
 static int check_watchdog() {
     if (G.host_error && *(volatile uint32_t *)G.host_error) {
         *(volatile uint32_t *)G.host_error = 0; // reported once; the caller decides whether to go on

@@ -201,6 +201,15 @@ int dlnb_batch_end(float *ms);
  * recent BLOCKING call (those use an internal slot, never one of the caller's) */
 int dlnb_slot_elapsed(dlnb_comm_t c, int slot, float *ms);
 
+/* ---- another library's collectives on the communication stream (comparison builds only) --------
+ * No reference counterpart. The `nccl` build (cpp/proxy_classes.hpp: CCLCommunicator, what the reference's
+ * CCLCommunicator :135-253 does) enqueues ncclAllReduce & co. itself; these two calls give that work the
+ * ordering and the slot bookkeeping a collective of this library gets: begin = wait for the compute enqueued
+ * so far, start the slot's timer, hand out the stream (a cudaStream_t); end = stop the timer and record the
+ * completion dlnb_wait / dlnb_waitall look at. The product path never calls them. Not capturable. */
+int dlnb_foreign_begin(dlnb_comm_t c, int slot, void **cuda_stream);
+int dlnb_foreign_end(dlnb_comm_t c, int slot);
+
 /* ---- whole-iteration CUDA graphs ---------------------------------------------------
  * Added (no reference counterpart). For launch-bound configurations (vit_h with 4000 buckets:
  * 9 us of compute per bucket against ~30 us of host launch work) one proxy iteration —

@@ -112,3 +112,21 @@ def test_hybrid_2d_on_4_gpus_two_pipelines():
     sec = parse_sections(res.stdout)["dp_pp"]
     assert sec["json_data"]["dp_size"] == 2 and [sec["rank_outputs"][r]["stage_id"] for r in range(4)] == [0, 1, 0, 1]
     assert len(sec["rank_outputs"][0]["pp_comm_time"]) == 3 * 2 * 4  # runs x directions x micro-batches
+
+
+def test_nccl_comparison_build_on_2_gpus():
+    """The `nccl` comparison build (same drivers, collectives through NCCL as in the reference's CCLCommunicator): runs, reports
+    backend NCCL, and stays near the lower bound on a compute-dominated configuration."""
+    if GPU_COUNT < 2:
+        pytest.skip("needs 2 GPUs")
+    exe = os.path.join(ROOT, "bin", "nccl", "cpp", "data_parallel", "dp")
+    if not os.path.exists(exe):
+        pytest.skip("nccl build not present (no nccl.h at build time)")
+    from dlnetbench_b200.parser import parse_sections
+
+    res = subprocess.run([os.path.join(ROOT, "bin", "dlnb_launch"), "-n", "2", exe, "gpt2_l_16_bfloat16", "10", ".", "-t", "fp16", "-r", "3"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    g = parse_sections(res.stdout)["dp"]["json_data"]
+    assert g["backend"] == "NCCL" and g["world_size"] == 2
+    assert 1.0 <= g["ratio_to_lower_bound"] < 1.5, g["ratio_to_lower_bound"]

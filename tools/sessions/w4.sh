@@ -14,4 +14,10 @@ timeout 300 $L python tools/sweep.py --op reduce_scatter --dtype f16 --algo 3 --
 timeout 300 $L python tools/sweep.py --op allgather --dtype f16 --ctas 64,128 $S --out $O/sweep_ag.json > $O/sweep_ag.log 2>&1
 timeout 300 $L python tools/sweep.py --op allgather --dtype f16 --algo 3 --mc-ctas 16,32,64 $S --out $O/sweep_agm.json > $O/sweep_agm.log 2>&1
 timeout 300 $L python tools/stress.py --launches 30000 --out $O/stress.json > $O/stress.log 2>&1; echo "stress rc=$?" | tee -a $O/summary.txt
+(ncu --query-metrics 2>/dev/null | grep -i "nvl" | head -40) > $O/ncu_nvl_metrics.txt 2>&1
+timeout 200 ncu --metrics nvlrx__bytes.sum,nvltx__bytes.sum,gpu__time_duration.sum -k regex:copy_kernel -c 6 --csv --log-file $O/ncu_nvl_peer_copy.csv bin/peer_copy_peak --gpus 2 --reps 1 > $O/ncu_nvl_peer_copy.log 2>&1; echo "ncu nvl rc=$?" | tee -a $O/summary.txt
+for op in allreduce allgather reduce_scatter; do timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29520 tools/nccl_compare.py --op $op --min-bytes 4096 --max-bytes 1073741824 --out $O/nccl_w4_$op.json > $O/nccl_w4_$op.log 2>&1; done
+timeout 300 $L bin/nccl/cpp/data_parallel/dp llama3_8b_64_bfloat16 240 . -t fp16 -w 1 -r 1 > $O/proxy_nccl_dp_llama8b.txt 2>&1; echo "nccl dp rc=$?" | tee -a $O/summary.txt
+timeout 300 $L bin/nccl/cpp/data_parallel/fsdp llama3_8b_64_bfloat16 32 4 . -t fp16 -w 1 -r 1 > $O/proxy_nccl_fsdp_llama8b.txt 2>&1; echo "nccl fsdp rc=$?" | tee -a $O/summary.txt
+DLNB_LOOP_ITERS=50 timeout 300 $L bin/nccl/cpp/data_parallel/dp_loop vit_h_128_bfloat16 1000 . -t fp32 -w 3 > $O/proxy_nccl_dploop_vith1000.txt 2>&1; echo "nccl dp_loop rc=$?" | tee -a $O/summary.txt
 cat $O/summary.txt; tail -2 $O/mg_worker_quick.txt
