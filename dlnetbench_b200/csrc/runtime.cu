@@ -944,9 +944,10 @@ static int pick_grid(long want, long want_mc, int dtype, int op, int n, int thre
     } else if (n == 1) {
         g = (long)G.sms * 4;
     } else if (is_switch_op(op)) {
-        // the switch does the adding / replicating: few CTAs saturate the links. Measured (profiles/):
-        // 16 CTAs best on 8 GPUs (more is slower), 32 on 4 (16 leaves a quarter of the rate unused)
-        g = want_mc > 0 ? want_mc : (n >= 8 ? 16 : 32);
+        // the switch does the adding / replicating: few CTAs saturate it. Measured (profiles/r02/w4, w8): 16 CTAs
+        // best on 4 and on 8 GPUs at every size >= 64 MiB (4 GPUs, 1 GiB: 695 / 677 / 616 GB/s with 16 / 32 / 48)
+        (void)n;
+        g = want_mc > 0 ? want_mc : 16;
     } else if (op == OP_AR2 && n == 2) {
         g = 64; // measured on 2 GPUs (profiles/r02): 632 / 666 / 676 GB/s at 64 MiB / 256 MiB / 1 GiB with 64 CTAs, 587 / 653 / 671 with 128
     } else {

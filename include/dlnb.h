@@ -101,7 +101,7 @@ int dlnb_comm_destroy(dlnb_comm_t c);
 int dlnb_comm_rank(dlnb_comm_t c);
 int dlnb_comm_size(dlnb_comm_t c);
 /* tuning knobs: "ctas" (CTAs per collective kernel), "mc_ctas" (the same for the in-switch
- * kernels; 0 = 16 on 8 ranks, 32 below), "threads", "algo" (dlnb_algo; DLNB_ALGO_MULTIMEM also
+ * kernels; 0 = 16), "threads", "algo" (dlnb_algo; DLNB_ALGO_MULTIMEM also
  * sends allgather / reduce-scatter through the switch where the chunks are 16-byte aligned),
  * "twoshot_min_bytes" / "multimem_min_bytes" (AUTO thresholds), "timeout_ms" (flag-spin watchdog). */
 int dlnb_comm_set(dlnb_comm_t c, const char *key, long value);
