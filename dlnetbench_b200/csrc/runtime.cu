@@ -161,7 +161,9 @@ struct dlnb_comm {
     std::vector<uint32_t> recv_seq;
     std::vector<char> slot_used;
     long ctas = 0, threads = 512, algo = DLNB_ALGO_AUTO, twoshot_min_bytes = -1 /* auto: 2 MiB / n */, timeout_ms = 30000,
-         multimem_min_bytes = 512 << 10, mc_ctas = 0 /* grid of the in-switch kernels; 0 = by group size */;
+         multimem_min_bytes = 512 << 10, mc_ctas = 0 /* grid of the in-switch kernels; 0 = by group size */,
+         hybrid_pct = 0 /* share (percent) of a large allreduce that goes through the switch while the rest goes peer to peer */,
+         hybrid_min_bytes = 32 << 20;
 };
 
 static constexpr int MAX_COMMS = 64;
@@ -788,6 +790,7 @@ extern "C" int dlnb_comm_create(const int *ranks, int nranks, int num_slots, int
     if (const char *v = getenv("DLNB_TWOSHOT_MIN_BYTES")) c->twoshot_min_bytes = atol(v);
     if (const char *v = getenv("DLNB_MULTIMEM_MIN_BYTES")) c->multimem_min_bytes = atol(v);
     if (const char *v = getenv("DLNB_MC_CTAS")) c->mc_ctas = atol(v);
+    if (const char *v = getenv("DLNB_HYBRID_PCT")) c->hybrid_pct = std::min(100L, std::max(0L, atol(v)));
     G.comms.push_back(c);
     *out = c;
     return 0;
@@ -819,6 +822,10 @@ extern "C" int dlnb_comm_set(dlnb_comm_t c, const char *key, long value) {
     else if (!strcmp(key, "twoshot_min_bytes")) c->twoshot_min_bytes = value;
     else if (!strcmp(key, "multimem_min_bytes")) c->multimem_min_bytes = value;
     else if (!strcmp(key, "mc_ctas")) c->mc_ctas = value;
+    else if (!strcmp(key, "hybrid_pct")) {
+        if (value < 0 || value > 100) return fail("dlnb_comm_set: hybrid_pct %ld not in 0..100", value);
+        c->hybrid_pct = value;
+    } else if (!strcmp(key, "hybrid_min_bytes")) c->hybrid_min_bytes = value;
     else if (!strcmp(key, "timeout_ms")) c->timeout_ms = value;
     else return fail("dlnb_comm_set: unknown key %s", key);
     return 0;
@@ -831,6 +838,8 @@ extern "C" long dlnb_comm_get(dlnb_comm_t c, const char *key) {
     if (!strcmp(key, "twoshot_min_bytes")) return c->twoshot_min_bytes;
     if (!strcmp(key, "multimem_min_bytes")) return c->multimem_min_bytes;
     if (!strcmp(key, "mc_ctas")) return c->mc_ctas;
+    if (!strcmp(key, "hybrid_pct")) return c->hybrid_pct;
+    if (!strcmp(key, "hybrid_min_bytes")) return c->hybrid_min_bytes;
     if (!strcmp(key, "timeout_ms")) return c->timeout_ms;
     if (!strcmp(key, "id")) return c->id;
     return -1;
@@ -1005,6 +1014,68 @@ static int mark_exclusive_on_lane0() {
     return 0;
 }
 
+// what this rank sees of one collective on `lane` (peer mappings of the two buffers, flag rows, generations)
+static int make_view(dlnb_comm *c, int op, int lane, const void *send, void *recv, const char *mc_s, char *mc_r, RankView &v) {
+    memset(&v, 0, sizeof(v));
+    v.rank = c->me;
+    v.nranks = c->n;
+    for (int i = 0; i < c->n; ++i) {
+        char *s = translate(send, c->ranks[i]);
+        char *r = translate(recv, c->ranks[i]);
+        if (!s || !r) return fail("buffer %p/%p is not in the symmetric arena (use dlnb_symm_alloc)", send, recv);
+        v.send[i] = s;
+        v.recv[i] = r;
+        v.flags[i] = (uint32_t *)translate(G.flag_area + (size_t)(c->id * 2 + lane) * FLAG_BYTES_PER_COMM, c->ranks[i]);
+    }
+    v.mc_send = is_switch_op(op) ? mc_s : nullptr;
+    v.mc_recv = is_switch_op(op) ? mc_r : nullptr;
+    v.strict = (int)G.strict_barriers;
+    v.shift_overlap = (int)G.shift_overlap;
+    v.ctl = G.ctl + (c->id * 2 + lane);
+    v.host_error = G.host_error_dev;
+    v.timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;
+    return 0;
+}
+
+// A large allreduce split between the switch and the links: the first `hybrid_pct` percent (whole 8 KiB units) go
+// through the in-switch kernel on lane 0, the rest through the fused two-shot kernel on lane 1, at the same time. The
+// in-switch path stalls near 540 GB/s of wire rate per direction; the peer-to-peer path uses what the links have left.
+// Both are exclusive: ordered after everything issued before, and everything issued later is ordered after both.
+static int coll_hybrid(dlnb_comm *c, const void *send, void *recv, size_t count, int slot, const char *mc_s, char *mc_r) {
+    const size_t esz = dtype_size(c->dtype);
+    const size_t unit = 8192 / esz;
+    const size_t c_mm = count * (size_t)c->hybrid_pct / 100 / unit * unit, c_pp = count - c_mm;
+    const int threads = (int)c->threads;
+    int g_mm = 1, g_pp = 1;
+    if (pick_grid(0, c->mc_ctas, c->dtype, OP_ARM, c->n, threads, work_bytes(OP_ARM, c->n, c_mm, esz), &g_mm)) return 1;
+    if (pick_grid(64, 0, c->dtype, OP_AR2, c->n, threads, work_bytes(OP_AR2, c->n, c_pp, esz), &g_pp)) return 1;
+    if (join_streams()) return 1;
+    if (drain_lane1_into_lane0()) return 1;
+    CU_TRY(cudaEventRecord(G.ev_excl, G.s_comm)); // lane 1 starts after everything lane 0 has, too
+    CU_TRY(cudaStreamWaitEvent(G.s_comm2, G.ev_excl, 0));
+    G.excl_pending = false;
+    const bool timed = G.slot_timing && !G.capturing;
+    if (timed) CU_TRY(cudaEventRecord(c->ev_start[slot], G.s_comm));
+    EmuViews ev;
+    if (make_view(c, OP_ARM, 0, send, recv, mc_s, mc_r, ev.v[0])) return 1;
+    cudaError_t e = launch_dtype(c->dtype, OP_ARM, c->n, dim3(g_mm, 1, 1), threads, G.s_comm, ev, c_mm, false);
+    if (e != cudaSuccess) return fail("collective launch failed: %s", cudaGetErrorString(e));
+    if (make_view(c, OP_AR2, 1, (const char *)send + c_mm * esz, (char *)recv + c_mm * esz, nullptr, nullptr, ev.v[0])) return 1;
+    e = launch_dtype(c->dtype, OP_AR2, c->n, dim3(g_pp, 1, 1), threads, G.s_comm2, ev, c_pp, false);
+    if (e != cudaSuccess) return fail("collective launch failed: %s", cudaGetErrorString(e));
+    G.launches += 2;
+    if (G.capturing) G.comm2_in_capture = true;
+    CU_TRY(cudaEventRecord(G.ev_lane1, G.s_comm2)); // the slot is complete when both halves are
+    CU_TRY(cudaStreamWaitEvent(G.s_comm, G.ev_lane1, 0));
+    G.lane1_dirty = false;
+    if (mark_exclusive_on_lane0()) return 1;
+    if (timed) CU_TRY(cudaEventRecord(c->ev_end[slot], G.s_comm));
+    CU_TRY(cudaEventRecord(c->ev_done[slot], G.s_comm));
+    c->slot_timed[slot] = timed ? 1 : 0;
+    c->slot_used[slot] = 1;
+    return 0;
+}
+
 static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count, int slot) {
     NEED_INIT();
     if (!c) return fail("null communicator");
@@ -1054,6 +1125,8 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
             else if (op == OP_RS && mc_s) op = OP_RSM;
         }
     }
+    if (op == OP_ARM && c->hybrid_pct > 0 && c->hybrid_pct < 100 && G.lanes > 1 && count * esz >= (size_t)c->hybrid_min_bytes)
+        return coll_hybrid(c, send, recv, count, slot, mc_s, mc_r);
     // Grid first: it decides the lane. Small allreduces (<= 64 CTAs, so two of them plus the spin
     // kernel are always co-resident) alternate between the two lanes; everything else is
     // exclusive on lane 0.
@@ -1079,25 +1152,7 @@ static int coll(dlnb_comm *c, int op, const void *send, void *recv, size_t count
     if (timed) CU_TRY(cudaEventRecord(c->ev_start[slot], st));
     if (count) {
         EmuViews ev;
-        RankView &v = ev.v[0];
-        memset(&v, 0, sizeof(v));
-        v.rank = c->me;
-        v.nranks = c->n;
-        for (int i = 0; i < c->n; ++i) {
-            char *s = translate(send, c->ranks[i]);
-            char *r = translate(recv, c->ranks[i]);
-            if (!s || !r) return fail("buffer %p/%p is not in the symmetric arena (use dlnb_symm_alloc)", send, recv);
-            v.send[i] = s;
-            v.recv[i] = r;
-            v.flags[i] = (uint32_t *)translate(G.flag_area + (size_t)(c->id * 2 + lane) * FLAG_BYTES_PER_COMM, c->ranks[i]);
-        }
-        v.mc_send = is_switch_op(op) ? mc_s : nullptr;
-        v.mc_recv = is_switch_op(op) ? mc_r : nullptr;
-        v.strict = (int)G.strict_barriers;
-        v.shift_overlap = (int)G.shift_overlap;
-        v.ctl = G.ctl + (c->id * 2 + lane);
-        v.host_error = G.host_error_dev;
-        v.timeout_ns = (unsigned long long)c->timeout_ms * 1000000ull;
+        if (make_view(c, op, lane, send, recv, mc_s, mc_r, ev.v[0])) return 1;
         cudaError_t e = launch_dtype(c->dtype, op, c->n, dim3(grid, 1, 1), threads, st, ev, count, false, c->n == 1 && G.pdl && !G.capturing);
         if (e != cudaSuccess) return fail("collective launch failed: %s", cudaGetErrorString(e));
         G.launches++;

@@ -77,6 +77,24 @@ def run(rank: int, world: int, quick: bool = True, dtypes=(capi.F32, capi.F16, c
                             bad = capi.verify_sum_pattern(recv.data, count, 0, dtype, kind, seed, g)
                             t.expect(bad == 0, f"allreduce {gname} dtype={dtype} algo={algo} count={count} kind={kind}: {bad} mismatches")
                     comm.set("algo", capi.ALGO_AUTO)
+                    # split allreduce: part through the switch on lane 0, the rest peer to peer on lane 1, at the same time
+                    if has_mc and whole and count >= 65536 + 17:
+                        comm.set("algo", capi.ALGO_MULTIMEM)
+                        comm.set("hybrid_min_bytes", 0)
+                        for pct in (70, 30):
+                            comm.set("hybrid_pct", pct)
+                            recv.fill(capi.PAT_ZERO)
+                            comm.Iallreduce(send.data, recv.data, count, 3)
+                            comm.Wait(3)
+                            if kind == capi.PAT_INT:
+                                bad = capi.verify_sum_pattern(recv.data, count, 0, dtype, kind, seed, g)
+                            else:
+                                bad, _ = capi.verify_sum_pattern_tol(recv.data, count, 0, dtype, kind, seed, g, 2 * (n - 1) * EPS[dtype])
+                            t.multimem_cases += 1
+                            t.expect(bad == 0, f"split allreduce {pct}% in-switch dtype={dtype} count={count} kind={kind}: {bad} mismatches")
+                        comm.set("hybrid_pct", 0)
+                        comm.set("hybrid_min_bytes", 32 << 20)
+                        comm.set("algo", capi.ALGO_AUTO)
                     # in place (send == recv): the runtime must keep it off the one-shot kernel
                     if kind == capi.PAT_UNIFORM and count <= 1_000_003:
                         inplace = capi.Tensor(count, dtype)

@@ -103,7 +103,10 @@ int dlnb_comm_size(dlnb_comm_t c);
 /* tuning knobs: "ctas" (CTAs per collective kernel), "mc_ctas" (the same for the in-switch
  * kernels; 0 = 16), "threads", "algo" (dlnb_algo; DLNB_ALGO_MULTIMEM also
  * sends allgather / reduce-scatter through the switch where the chunks are 16-byte aligned),
- * "twoshot_min_bytes" / "multimem_min_bytes" (AUTO thresholds), "timeout_ms" (flag-spin watchdog). */
+ * "twoshot_min_bytes" / "multimem_min_bytes" (AUTO thresholds), "timeout_ms" (flag-spin watchdog),
+ * "hybrid_pct" (0..100, default 0 = off) / "hybrid_min_bytes" (default 32 MiB): an in-switch allreduce of at least
+ * hybrid_min_bytes sends only the first hybrid_pct percent through the switch and the rest through the peer-to-peer
+ * two-shot kernel on the second communication lane, both at the same time. */
 int dlnb_comm_set(dlnb_comm_t c, const char *key, long value);
 long dlnb_comm_get(dlnb_comm_t c, const char *key);
 
