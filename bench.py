@@ -368,6 +368,8 @@ def main():
     in_step = [comm.slot_ms(i) for i in range(a.buckets)]
     in_step_stats = over_ranks(statistics.median(in_step))
     in_step_mean = over_ranks(sum(in_step) / len(in_step))
+    k8 = min(8, a.buckets)
+    in_step_first, in_step_last = over_ranks(sum(in_step[:k8]) / k8), over_ranks(sum(in_step[-k8:]) / k8)
     buckets_verified += verify_all_buckets("after the timed steps")
 
     # ---- the dominant kernel alone: every bucket's allreduce back to back (16 GB of distinct inputs, nothing
@@ -526,7 +528,10 @@ def main():
             roof["nvlink_tx_GBps"] = traffic["data_tx_bytes_per_launch"] / (kern_avg_ms * 1e-3) / 1e9
             roof["nvlink_rx_GBps"] = traffic["data_rx_bytes_per_launch"] / (kern_avg_ms * 1e-3) / 1e9
     roof["avg_launch_ms_inside_step"] = {"median_per_rank": in_step_stats, "mean_per_rank": in_step_mean,
-                                         "note": "slot events of the last timed step; min / median / max over ranks"}
+                                         "first_8_buckets": in_step_first, "last_8_buckets": in_step_last,
+                                         "note": "slot events of the last timed step; min / median / max over ranks. The minimum is the kernel's own time beside "
+                                                 "the emulated compute; the maximum adds the wait for the rank whose %globaltimer runs slowest (the ranks start "
+                                                 "together, then drift apart by tens of ppm: the spread grows from the first to the last buckets)"}
     if world == 1:
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
