@@ -24,4 +24,6 @@ for cfg in b200 nccl; do
   DLNB_LOOP_ITERS=40 timeout 120 $L bin/$cfg/cpp/data_parallel/dp_loop vit_h_128_bfloat16 1000 . -t fp32 -w 3 > $O/proxy_${cfg}_dploop_vith1000.txt 2>&1; echo "$cfg dp_loop rc=$?" | tee -a $O/summary.txt
   timeout 120 $L bin/$cfg/cpp/data_parallel/fsdp gpt2_l_16_bfloat16 36 8 . -t fp16 -w 2 -r 5 > $O/proxy_${cfg}_fsdp_gpt2l.txt 2>&1; echo "$cfg fsdp rc=$?" | tee -a $O/summary.txt
 done
+(ncu --query-metrics 2>/dev/null | grep -i "nvl" | head -40) > $O/ncu_nvl_metrics.txt 2>&1
+timeout 120 ncu --metrics nvlrx__bytes.sum,nvltx__bytes.sum,gpu__time_duration.sum -k regex:copy_kernel -c 6 --csv --log-file $O/ncu_nvl_peer_copy.csv bin/peer_copy_peak --gpus 2 --reps 1 > $O/ncu_nvl_peer_copy.log 2>&1; echo "ncu nvl rc=$?" | tee -a $O/summary.txt
 cat $O/summary.txt; tail -2 $O/mg_worker_quick.txt
