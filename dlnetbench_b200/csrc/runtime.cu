@@ -232,6 +232,7 @@ struct State {
     void *flush_buf = nullptr;
     size_t flush_bytes = 0;
     unsigned long long *d_scalar = nullptr; // 8-byte device scratch for verify/checksum
+    unsigned *d_worst = nullptr;            // 4-byte device scratch of the tolerance verifier
 };
 static State G;
 
@@ -458,6 +459,7 @@ extern "C" const char *dlnb_arena_kind(void) {
 extern "C" uint64_t dlnb_launch_count(void) { return G.launches; }
 extern "C" size_t dlnb_symm_bytes_in_use(void) { return G.bytes_in_use; }
 
+static int ensure_spin_stream();
 extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     if (G.inited) return fail("dlnb_init called twice");
     if (world < 1 || world > MAXR) return fail("world size %d not in 1..%d (one NVSwitch box)", world, MAXR);
@@ -559,6 +561,7 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
         G.spin_regs = fa.numRegs;
     }
     if (const char *v = getenv("DLNB_SPIN_MODE")) G.spin_mode = std::min(2L, std::max(0L, atol(v)));
+    if (G.spin_mode == SPIN_HBM && ensure_spin_stream()) return 1;
     if (const char *v = getenv("DLNB_SPIN_CTAS")) G.spin_ctas = std::max(0L, atol(v));
     if (const char *v = getenv("DLNB_SPIN_THREADS")) G.spin_threads = std::min(1024L, std::max(32L, atol(v)));
     if (const char *v = getenv("DLNB_STRICT_BARRIERS")) G.strict_barriers = atol(v) != 0;
@@ -623,6 +626,7 @@ extern "C" int dlnb_finalize(void) {
     if (G.emu_ctl) cudaFree(G.emu_ctl);
     if (G.flush_buf) cudaFree(G.flush_buf);
     if (G.d_scalar) cudaFree(G.d_scalar);
+    if (G.d_worst) cudaFree(G.d_worst);
     if (G.p2p_state) cudaFree(G.p2p_state);
     if (G.spin_stamps) cudaFree(G.spin_stamps);
     if (G.spin_sink) cudaFree(G.spin_sink);
@@ -670,6 +674,15 @@ extern "C" int dlnb_symm_free(void *ptr) {
     return arena_free(ptr);
 }
 
+// SPIN_HBM streams a buffer larger than L2: allocated on first use (1 GiB: eight times the L2)
+static int ensure_spin_stream() {
+    if (G.spin_stream) return 0;
+    G.spin_stream_vecs = ((size_t)1 << 30) / sizeof(uint4);
+    CU_TRY(cudaMalloc((void **)&G.spin_stream, G.spin_stream_vecs * sizeof(uint4)));
+    CU_TRY(cudaMemset(G.spin_stream, 0x11, G.spin_stream_vecs * sizeof(uint4)));
+    return 0;
+}
+
 extern "C" int dlnb_set(const char *key, long value) {
     if (!key) return fail("dlnb_set: null key");
     if (!strcmp(key, "spin_ctas")) G.spin_ctas = std::max(0L, value); // 0 = one CTA per SM
@@ -679,9 +692,7 @@ extern "C" int dlnb_set(const char *key, long value) {
         if (value == SPIN_HBM && !G.spin_stream) {
             NEED_INIT();
             if (G.capturing) return fail("dlnb_set: spin_mode cannot change inside a graph capture");
-            G.spin_stream_vecs = ((size_t)1 << 30) / sizeof(uint4); // 1 GiB: eight times the L2
-            CU_TRY(cudaMalloc((void **)&G.spin_stream, G.spin_stream_vecs * sizeof(uint4)));
-            CU_TRY(cudaMemset(G.spin_stream, 0x11, G.spin_stream_vecs * sizeof(uint4)));
+            if (ensure_spin_stream()) return 1;
         }
         G.spin_mode = value;
     } else if (!strcmp(key, "spin_smem")) {
@@ -1699,8 +1710,8 @@ extern "C" int dlnb_verify_sum_pattern_tol(const void *ptr, size_t count, size_t
     RankList rl;
     rl.n = nranks;
     for (int i = 0; i < nranks; ++i) rl.r[i] = ranks[i];
-    static unsigned *d_worst = nullptr;
-    if (!d_worst) CU_TRY(cudaMalloc((void **)&d_worst, sizeof(unsigned)));
+    if (!G.d_worst) CU_TRY(cudaMalloc((void **)&G.d_worst, sizeof(unsigned)));
+    unsigned *d_worst = G.d_worst;
     CU_TRY(cudaMemsetAsync(G.d_scalar, 0, sizeof(unsigned long long), G.s_comm));
     CU_TRY(cudaMemsetAsync(d_worst, 0, sizeof(unsigned), G.s_comm));
     if (count) {

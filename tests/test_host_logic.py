@@ -303,3 +303,42 @@ def test_bench_plumbing_world_size_2_gloo():
         p.join(60)
         assert p.exitcode == 0
     assert got == [(0, 11.0, 5.0), (1, 11.0, 5.0)]
+
+
+def test_link_counters_degrade_gracefully_without_nvml():
+    """No NVML / nvidia-smi (this container) or counters not exposed (the pool's boxes): ok is False and `why` says so — bench.py
+    then reports the reason in roofline.nvlink instead of a byte count."""
+    from dlnetbench_b200 import nvlink
+
+    lc = nvlink.LinkCounters(0)
+    if not lc.ok:
+        assert lc.why and ("nvml" in lc.why.lower() or "nvidia" in lc.why.lower())
+    d = nvlink.per_launch({"data_tx": 1000, "data_rx": 0}, {"data_tx": 21000, "data_rx": 4000}, 20)
+    assert d == {"data_tx_bytes_per_launch": 1000.0, "data_rx_bytes_per_launch": 200.0}
+
+
+def test_cpu_baseline_scale_follows_the_host_ram():
+    """bench.py sizes the reference's CPU run from the box: the whole workload when its fp32 buffers (2 x 4 x Model_Size bytes per
+    rank, dp.cpp:227-232) fit half of the available RAM, else the largest power-of-two fraction that does — and says which."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    m = 8_030_261_248  # llama3_8b
+    assert bench.pick_scale(m, 1, {"cores": 16, "mem_available_bytes": 206e9}) == 1      # 64 GB of 103 GB
+    assert bench.pick_scale(m, 2, {"cores": 16, "mem_available_bytes": 206e9}) == 2      # 128 GB does not fit 103 GB
+    assert bench.pick_scale(m, 8, {"cores": 128, "mem_available_bytes": 2e12}) == 1      # 514 GB of 1 TB
+    assert bench.pick_scale(m, 8, {"cores": 16, "mem_available_bytes": None}) == 64       # unknown RAM: 16 GB budget, 514 GB / 64 = 8 GB
+    res = bench.host_resources()
+    assert res["cores"] >= 1 and (res["mem_available_bytes"] is None or res["mem_available_bytes"] > 0)
+
+
+def test_selfcheck_and_session_tools_import_without_a_gpu():
+    import ast
+
+    for rel in ("dlnetbench_b200/selfcheck.py", "tools/stress.py", "tools/hybrid_probe.py", "tools/footprint_probe.py", "tools/sanitize_probe.py"):
+        ast.parse(open(os.path.join(ROOT, rel)).read())
+    from dlnetbench_b200 import selfcheck
+
+    assert selfcheck.EPS[1] == 2.0 ** -10
