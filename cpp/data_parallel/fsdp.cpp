@@ -28,6 +28,14 @@ static b200::HostTimer timer_allgather, timer_reduce_scatter, timer_allgather_wa
 static bool blocking_compute = false;
 static bool in_graph_capture = false;
 static float first_allgather_ms = 0.f; // device time of the exposed Allgather of unit 0 (most recent iteration)
+// what was LEFT of each prefetch Allgather after the compute it was hidden behind had ended (device-timed, ms): the
+// reference's meaning of allgather_wait_fwd / _bwd, kept beside the host timers because compute is asynchronous here
+static std::vector<float> exposed_wait_fwd_ms, exposed_wait_bwd_ms;
+static float exposed_after_mark(ProxyCommunicator *comm, int slot) {
+    float ms = 0.f;
+    if (!in_graph_capture) b200::check(dlnb_slot_exposed(static_cast<ProxyBackend *>(comm)->handle(), slot, &ms), "slot exposed");
+    return ms;
+}
 
 static inline void emulate_compute(float usec) {
     b200::check(dlnb_compute_spin((double)(uint64_t)usec), "compute spin"); // usleep(float) truncates
@@ -53,9 +61,11 @@ void run_fsdp(Tensor<T, device> **shard_params, Tensor<T, device> *layer_params,
     for (unsigned u = 0; u + 1 < num_units; u++) {
         unit_comm->Iallgather(shard_params[u + 1]->data, shard_count(u + 1), layer_params->data, shard_count(u + 1), u + 1);
         emulate_compute(fwd_rt_whole_unit);
+        b200::check(dlnb_compute_mark(), "compute mark");
         timer_allgather_wait_fwd.start();
         unit_comm->Wait(u + 1);
         timer_allgather_wait_fwd.stop();
+        exposed_wait_fwd_ms.push_back(exposed_after_mark(unit_comm, (int)u + 1));
     }
 
     // backward, last unit first: gather unit u-1, compute unit u, scatter-reduce its gradients
@@ -63,6 +73,7 @@ void run_fsdp(Tensor<T, device> **shard_params, Tensor<T, device> *layer_params,
         if (u > 0)
             unit_comm->Iallgather(shard_params[u - 1]->data, shard_count(u - 1), layer_params->data, shard_count(u - 1), u - 1);
         emulate_compute(bwd_rt_whole_unit);
+        b200::check(dlnb_compute_mark(), "compute mark");
 
         timer_reduce_scatter.start();
         unit_comm->Reduce_Scatter_block(layer_params->data, shard_params[u]->data, shard_count(u));
@@ -74,6 +85,7 @@ void run_fsdp(Tensor<T, device> **shard_params, Tensor<T, device> *layer_params,
             timer_allgather_wait_bwd.start();
             unit_comm->Wait(u - 1);
             timer_allgather_wait_bwd.stop();
+            exposed_wait_bwd_ms.push_back(exposed_after_mark(unit_comm, u - 1));
         }
     }
     if (num_replicas > 1) {
@@ -101,6 +113,8 @@ static void clear_timers() {
     timer_allgather_wait_bwd.clear();
     timer_reduce_scatter.clear();
     timer_barrier.clear();
+    exposed_wait_fwd_ms.clear();
+    exposed_wait_bwd_ms.clear();
 }
 
 template <typename T> static int proxy_main(const b200::Cli &cli, const b200::World &w) {
@@ -248,6 +262,8 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         .put("allgather_wait_fwd", timer_allgather_wait_fwd.vals)
         .put("allgather_wait_bwd", timer_allgather_wait_bwd.vals)
         .put("reduce_scatter", timer_reduce_scatter.vals)
+        .put("allgather_exposed_wait_fwd_ms", exposed_wait_fwd_ms)
+        .put("allgather_exposed_wait_bwd_ms", exposed_wait_bwd_ms)
         .put("barrier", timer_barrier.vals)
         .put("hostname", host_name)
         .put("rank", w.rank)
@@ -287,7 +303,8 @@ template <typename T> static int proxy_main(const b200::Cli &cli, const b200::Wo
         // allgather_wait_* time Wait() from the moment the host reaches it. The reference's host sleeps through
         // the compute first (usleep), so its timers hold only the wait that is LEFT; here compute is asynchronous
         // and the timers also contain the overlapped part, unless DLNB_BLOCKING_COMPUTE=1 makes the host wait
-        // for each spin like usleep does.
+        // for each spin like usleep does. The per-rank lists allgather_exposed_wait_{fwd,bwd}_ms hold the reference's meaning
+        // either way: what was left of the allgather after the compute had ended, from device events.
         .put("wait_timers_include_overlap", !blocking_compute && !cli.graph)
         .put("kernel_launches", (uint64_t)dlnb_launch_count());
     fsdp.emit();

@@ -72,6 +72,8 @@ def _declare(L: C.CDLL) -> None:
         "dlnb_comm_get": (C.c_long, [vp, cp]),
         "dlnb_compute_spin": (i, [C.c_double]),
         "dlnb_compute_sync": (i, []),
+        "dlnb_compute_mark": (i, []),
+        "dlnb_slot_exposed": (i, [vp, i, C.POINTER(C.c_float)]),
         "dlnb_spin_calibrate": (i, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "dlnb_set": (i, [cp, C.c_long]),
         "dlnb_get": (C.c_long, [cp]),

@@ -176,7 +176,8 @@ struct State {
     ArenaKind kind = ARENA_LOCAL;
     Bootstrap boot;
     cudaStream_t s_compute = nullptr, s_comm = nullptr, s_comm2 = nullptr, s_copy = nullptr, s_out = nullptr;
-    cudaEvent_t ev_gate = nullptr, ev_out = nullptr;
+    cudaEvent_t ev_gate = nullptr, ev_out = nullptr, ev_mark = nullptr;
+    bool mark_set = false;
     bool out_dirty = false; // device -> host copies enqueued on s_out that the end of the iteration must wait for
     // Two communication lanes: consecutive small allreduces alternate between s_comm (lane 0) and
     // s_comm2 (lane 1) so their barrier latencies overlap; everything else runs on lane 0 alone.
@@ -542,6 +543,7 @@ extern "C" int dlnb_init(int rank, int world, int device, const char *session) {
     CU_TRY(cudaStreamCreateWithPriority(&G.s_out, cudaStreamNonBlocking, lo));
     CU_TRY(cudaEventCreateWithFlags(&G.ev_gate, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&G.ev_out, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreate(&G.ev_mark));
     CU_TRY(cudaEventCreateWithFlags(&G.ev_join, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&G.ev_copy, cudaEventDisableTiming));
     CU_TRY(cudaEventCreate(&G.ev_iter0));
@@ -641,6 +643,7 @@ extern "C" int dlnb_finalize(void) {
     cudaStreamDestroy(G.s_out);
     cudaEventDestroy(G.ev_gate);
     cudaEventDestroy(G.ev_out);
+    cudaEventDestroy(G.ev_mark);
     cudaEventDestroy(G.ev_join);
     cudaEventDestroy(G.ev_copy);
     cudaEventDestroy(G.ev_iter0);
@@ -880,6 +883,30 @@ extern "C" int dlnb_compute_sync(void) {
     NEED_INIT();
     if (G.capturing) return 0;
     CU_TRY(cudaStreamSynchronize(G.s_compute));
+    return 0;
+}
+// "The compute enqueued so far ends HERE": a timestamp on the compute stream, against which dlnb_slot_exposed()
+// measures how much of a collective was still running after that compute had finished — the part of a Wait() that
+// the reference's host, which sleeps through the compute first (usleep), would actually have waited.
+extern "C" int dlnb_compute_mark(void) {
+    NEED_INIT();
+    if (G.capturing) return 0;
+    CU_TRY(cudaEventRecord(G.ev_mark, G.s_compute));
+    G.mark_set = true;
+    return 0;
+}
+extern "C" int dlnb_slot_exposed(dlnb_comm_t c, int slot, float *ms) {
+    NEED_INIT();
+    if (!c || !ms) return fail("null argument");
+    *ms = 0.f;
+    if (G.capturing || !G.mark_set) return 0;
+    if (slot == -1) slot = c->num_slots;
+    if (slot < 0 || slot > c->num_slots || !c->slot_used[slot] || !c->slot_timed[slot]) return 0;
+    CU_TRY(cudaEventSynchronize(G.ev_mark));
+    CU_TRY(cudaEventSynchronize(c->ev_end[slot]));
+    float d = 0.f;
+    CU_TRY(cudaEventElapsedTime(&d, G.ev_mark, c->ev_end[slot]));
+    *ms = d > 0.f ? d : 0.f;
     return 0;
 }
 extern "C" int dlnb_spin_calibrate(double *overhead_us, double *slope) {

@@ -79,6 +79,9 @@ def fsdp_metrics_df(section: dict, job_vars: dict | None = None, network: str = 
             continue
         barriers, ag = r.get("barrier", []), r.get("allgather", [])
         wf, wb, rs = r.get("allgather_wait_fwd", []), r.get("allgather_wait_bwd", []), r.get("reduce_scatter", [])
+        # b200 addition: the part of each prefetch allgather that was still running when the compute hiding it had ended
+        # (device-timed, ms) — the reference's meaning of the two wait timers (its host sleeps through the compute first)
+        xf, xb = r.get("allgather_exposed_wait_fwd_ms", []), r.get("allgather_exposed_wait_bwd_ms", [])
         device = r.get("device_runtimes_ms", [])
         host = r.get("hostname", "unknown")
         units = base["num_units"] or max(len(rs) // n_runs, 1)
@@ -95,6 +98,8 @@ def fsdp_metrics_df(section: dict, job_vars: dict | None = None, network: str = 
                 comm_rows.append({**base, "rank": rank, "hostname": host, "run": i, "unit_idx": u,
                                   "allgather_wait_fwd": wf[kf] if u >= 1 and kf < len(wf) else 0,
                                   "allgather_wait_bwd": wb[kb] if u <= units - 2 and kb < len(wb) else 0,
+                                  "allgather_exposed_wait_fwd_ms": xf[kf] if u >= 1 and kf < len(xf) else 0,
+                                  "allgather_exposed_wait_bwd_ms": xb[kb] if u <= units - 2 and kb < len(xb) else 0,
                                   "reduce_scatter": rs[ks] if ks < len(rs) else 0})
     return pd.DataFrame(runtime_rows), pd.DataFrame(comm_rows)
 

@@ -115,6 +115,12 @@ long dlnb_comm_get(dlnb_comm_t c, const char *key);
  * calibrated %globaltimer spin kernel on the compute stream. Asynchronous. */
 int dlnb_compute_spin(double usec);
 int dlnb_compute_sync(void);
+/* dlnb_compute_mark: timestamp "the compute enqueued so far ends here" on the compute stream. dlnb_slot_exposed: how long
+ * the collective recorded in `slot` kept running after that mark (0 if it finished earlier) — the wait that is LEFT after
+ * the compute, which is what the reference's timers around Wait() hold (its host sleeps through the compute first:
+ * fsdp.cpp:103-107,120-139). Both are no-ops inside a graph capture. */
+int dlnb_compute_mark(void);
+int dlnb_slot_exposed(dlnb_comm_t c, int slot, float *ms);
 /* Consecutive spins chain: one that starts within "spin_slack_ns" (default 8000) of the
  * previous spin's nominal end counts from that end, so a chain of k spins lasts the sum of
  * the requests, not k launch gaps more.
