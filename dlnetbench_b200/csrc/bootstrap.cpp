@@ -79,9 +79,15 @@ std::string Bootstrap::connect(int rank, int world, const std::string &session, 
         peers_.assign(world, -1);
         for (int k = 1; k < world; ++k) {
             pollfd pf{listen_fd_, POLLIN, 0};
-            int pr = ::poll(&pf, 1, timeout_s * 1000);
+            int pr;
+            do { // a signal (profilers deliver them) interrupts poll: that is not a timeout
+                pr = ::poll(&pf, 1, timeout_s * 1000);
+            } while (pr < 0 && errno == EINTR);
             if (pr <= 0) return "rendezvous timeout: not all ranks connected to the hub";
-            int fd = ::accept(listen_fd_, nullptr, nullptr);
+            int fd;
+            do {
+                fd = ::accept(listen_fd_, nullptr, nullptr);
+            } while (fd < 0 && errno == EINTR);
             if (fd < 0) return errstr("accept");
             int r = -1;
             if (!recv_all(fd, &r, sizeof(r)) || r <= 0 || r >= world || peers_[r] != -1) {

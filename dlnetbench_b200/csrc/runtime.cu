@@ -1360,6 +1360,8 @@ static int p2p(dlnb_comm *c, bool is_send, const void *buf, size_t count, int pe
     if (count && !(b >= (const char *)G.window[G.rank] && b + bytes <= (const char *)G.window[G.rank] + G.va_used))
         return fail("buffer %p is not in the symmetric arena (use dlnb_symm_alloc)", buf);
     if (G.capturing) return fail("send/recv cannot be captured into a graph");
+    if (c->recv_src[slot] >= 0)
+        return fail("slot %d still holds a posted receive that has not been waited for (one pending operation per slot)", slot);
     if (join_streams()) return 1;
     if (drain_lane1_into_lane0()) return 1; // ordered on lane 0 behind everything, like allgather / reduce-scatter
     P2PBox *mine = G.p2p_boxes + wpeer;                                // my box for this peer

@@ -39,7 +39,7 @@ def main():
     capi.init(rank, world)
     dt = {"f32": capi.F32, "f16": capi.F16, "bf16": capi.BF16}[a.dtype]
     esz = capi.DTYPE_SIZE[dt]
-    comm = capi.B200Communicator(list(range(world)), num_slots=a.iters, dtype=dt)
+    comm = capi.B200Communicator(list(range(world)), num_slots=2 * a.iters, dtype=dt)
     comm.set("algo", a.algo)
     comm.set("threads", a.threads)
     capi.set_option("strict_barriers", a.strict)
@@ -63,8 +63,8 @@ def main():
         elif a.op == "reduce_scatter":
             capi.check(capi.lib().dlnb_ireduce_scatter(comm.h, s.data, r.data, rc, i))
         else:  # ring exchange: every rank receives from its left and sends to its right
-            comm.Irecv(r.data, rc, prv, i)
-            comm.Isend(s.data, sc, nxt, i)
+            comm.Irecv(r.data, rc, prv, i)  # a slot holds ONE pending operation: the send gets a slot of its own
+            comm.Isend(s.data, sc, nxt, a.iters + i)
 
     rows = []
     ladder = []
@@ -95,7 +95,7 @@ def main():
             for rep in range(2):  # first pass = warm-up
                 for i in range(a.iters):
                     issue(send[i % nbuf], recv[i % nbuf], sc, rc, i)
-                comm.WaitAll(a.iters)
+                comm.WaitAll(2 * a.iters)
             ms = sorted(comm.slot_ms(i) for i in range(a.iters))
             # device-only batch time: a spin blocks the communication stream while the host queues
             # the whole batch (no per-slot timing events), one event pair around the batch
@@ -106,7 +106,7 @@ def main():
             for i in range(a.iters):
                 issue(send[i % nbuf], recv[i % nbuf], sc, rc, i)
             b2b = capi.iter_end() / a.iters
-            comm.WaitAll(a.iters)  # posted receives count as outstanding until they have been waited for
+            comm.WaitAll(2 * a.iters)  # posted receives count as outstanding until they have been waited for
             wire = None
             if links:
                 from dlnetbench_b200 import nvlink
