@@ -496,7 +496,7 @@ def main():
         sub["dp_loop"] = dpl
         if world == 8:
             g = run_proxy(rank, world, local_rank, "fsdp_loop", ["llama3_70b_16_bfloat16", "80", "8", ".", "-t", "fp16", "-w", "1"],
-                          env_extra={"DLNB_LOOP_ITERS": "2"}, timeout=1200)
+                          env_extra={"DLNB_LOOP_ITERS": os.environ.get("DLNB_BENCH_C5_ITERS", "2")}, timeout=1200)
             sub["fsdp_loop"] = keep(g, common + ["num_units", "sharding_factor", "allgather_msg_size_bytes", "reducescatter_msg_size_bytes",
                                                  "reduce_scatter_last_ms", "reduce_scatter_busbw_GBps"])
             barrier()
