@@ -177,13 +177,19 @@ def host_resources():
     return {"cores": os.cpu_count() or 1, "mem_available_bytes": avail}
 
 
-def pick_scale(model_size, ranks, res):
-    """Largest sample (smallest divisor) of the workload whose fp32 buffers (2 x 4 bytes x Model_Size per rank,
-    dp.cpp:227-232) fit half of the box's available RAM. scale 1 = the whole workload, nothing extrapolated."""
+def pick_scale(model_size, ranks, res, lower_bound_ms=None, iterations=None, time_budget_s=600.0):
+    """Largest sample (smallest divisor) of the workload (a) whose fp32 buffers (2 x 4 bytes x Model_Size per rank, dp.cpp:227-232)
+    fit half of the box's available RAM and (b) whose run is expected to end within the time budget: `iterations` iterations of
+    lower bound x a communication factor seen on this pool's hosts (1.1 / 1.6 / 2.2 / 3.0 at 1 / 2 / 4 / 8 ranks).
+    scale 1 = the whole workload, nothing extrapolated; otherwise the caller reports "extrapolated": true and the scale."""
     budget = 0.5 * res["mem_available_bytes"] if res["mem_available_bytes"] else 16e9
     scale = 1
     while ranks * 2 * 4 * model_size / scale > budget:
         scale *= 2
+    if lower_bound_ms and iterations:
+        factor = {1: 1.1, 2: 1.6, 4: 2.2}.get(ranks, 3.0)
+        while iterations * lower_bound_ms * 1e-3 * factor / scale > time_budget_s:
+            scale *= 2
     return scale
 
 
@@ -250,7 +256,7 @@ def main():
         if rank != 0:
             return
         res = host_resources()
-        scale = pick_scale(st["modelSize"], a.gpus, res)
+        scale = pick_scale(st["modelSize"], a.gpus, res, lower_bound_ms, a.warmup + a.steps)
         r = run_reference_dp(a.model, a.buckets, a.gpus, a.warmup, a.steps, scale)
         if r is None:
             print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/dp missing or failed (build with make -C oracle ref where /root/reference is mounted)"}))

@@ -342,3 +342,16 @@ def test_selfcheck_and_session_tools_import_without_a_gpu():
     from dlnetbench_b200 import selfcheck
 
     assert selfcheck.EPS[1] == 2.0 ** -10
+
+
+def test_reference_arm_scale_respects_the_time_budget():
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("bench_mod2", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    m, lb, big = 8_030_261_248, 11258.759, {"cores": 128, "mem_available_bytes": 4e12}
+    assert bench.pick_scale(m, 1, big, lb, 25) == 1   # 25 x 11.26 s x 1.1 = 310 s
+    assert bench.pick_scale(m, 2, big, lb, 25) == 1   # 450 s
+    assert bench.pick_scale(m, 8, big, lb, 25) == 2   # 845 s -> half the workload, reported as extrapolated
+    assert bench.pick_scale(m, 8, big, lb, 4) == 1
