@@ -367,57 +367,83 @@ __device__ __forceinline__ void reduce_store_vec_shifted(const uint4 *const *src
     for (int p = 0; p < NSRC; ++p) s[p] = src[p];
 #pragma unroll
     for (int q = 0; q < NDST; ++q) d[q] = dst[q];
-    // A warp owns a window of 32*U aligned input vectors A[base .. base+32U) and produces the outputs that need
-    // only those: out[j] = shift(A[j], A[j+1]). A[j+1] comes from the right-hand lane by shuffle, for lane 31
-    // from lane 0 of the next row. Consecutive windows OVERLAP by `overlap` vectors (1, 2 or 8: the last output
-    // of a window needs the first vector of the next), so nothing is reloaded by a divergent lane and no extra
-    // registers are held; with 2 / 8 every window starts on a 32-byte sector / 128-byte line of the sources
-    // (a 512-byte warp load then touches 4 lines, not 5) at the price of 2 / 8 vectors loaded twice per window.
-    // Consecutive warps of a CTA take consecutive windows, CTAs stride by the grid.
-    const long long run = 32 * U - (long long)overlap;
-    // ... of the side that crosses NVLink: the sources of a pull, the destinations of a push (one local source)
-    const uintptr_t ref = NSRC == 1 ? (uintptr_t)d[0] : (uintptr_t)s[0];
-    const long long a0 = overlap > 1 ? (long long)((ref >> 4) & (overlap - 1)) : 0;
+    // out[j] = shift(A[j], A[j+1]) over the aligned input vectors A[0..nvec]. A warp owns a WINDOW of `rows` rows of 32
+    // consecutive vectors and walks it U rows at a time (U*NSRC loads in flight per thread); A[j+1] comes from the right-hand
+    // lane by shuffle, for lane 31 from lane 0 of the next row — across steps the last row of a step is CARRIED (one summed
+    // vector per thread) and finished when the next step's first row is there. Consecutive windows overlap by `overlap`
+    // vectors (the last outputs of a window need the first vector of the next): nothing is reloaded by a divergent lane, no
+    // raw data is held across steps, and with overlap 8 every window starts on a 128-byte line of the side that crosses
+    // NVLink (a 512-byte warp access then touches 4 lines, not 5). The redundant loads are overlap / (32*rows): 1.6 % for
+    // the 16-row windows of a large message, whatever U is (a window of only 32*U vectors, as in the first version of this
+    // path, cost 25 % at 7-8 ranks where U = 1). Windows shrink for small messages so that all warps get work.
     const unsigned lane = threadIdx.x & 31u;
     const long long wpc = blockDim.x >> 5, warp = threadIdx.x >> 5;
     const long long cta = (long long)(tid / blockDim.x), nctas = (long long)(nthr / blockDim.x);
     const long long nv = (long long)nvec;
+    long long rows = (nv / 32 + nctas * wpc - 1) / (nctas * wpc); // rows per warp if every warp took one window
+    rows = (min(max(rows, 1ll), 16ll) + U - 1) / U * U;           // 1..16, a multiple of U
+    const long long run = 32 * rows - (long long)overlap;         // outputs per window
+    // ... of the side that crosses NVLink: the sources of a pull, the destinations of a push (one local source)
+    const uintptr_t ref = NSRC == 1 ? (uintptr_t)d[0] : (uintptr_t)s[0];
+    const long long a0 = overlap > 1 ? (long long)((ref >> 4) & (overlap - 1)) : 0;
     for (long long r = cta * wpc + warp; r * run - a0 < nv; r += nctas * wpc) { // warp-uniform trip count
         const long long base = r * run - a0;
-        uint4 val[U][NSRC];
+        uint4 carry = make_uint4(0, 0, 0, 0);
+        for (long long row0 = 0; row0 < rows && base + row0 * 32 <= nv; row0 += U) { // warp-uniform
+            uint4 val[U][NSRC];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const long long i = min(max(base + u * 32 + (long long)lane, 0ll), nv); // A[nvec] is always readable
+            for (int u = 0; u < U; ++u) {
+                const long long i = min(max(base + (row0 + u) * 32 + (long long)lane, 0ll), nv); // A[nvec] is always readable
 #pragma unroll
-            for (int p = 0; p < NSRC; ++p) val[u][p] = ld_v4(s[p] + i);
-        }
-        uint4 cur[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            if (NSRC == 1) {
-                cur[u] = val[u][0];
-            } else {
-                Acc<T> a;
-                a.set(val[u][0]);
-#pragma unroll
-                for (int p = 1; p < NSRC; ++p) a.add(val[u][p]);
-                cur[u] = a.pack();
+                for (int p = 0; p < NSRC; ++p) val[u][p] = ld_v4(s[p] + i);
             }
-        }
+            uint4 cur[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            // lane l takes cur[u] of lane l+1; lane 31 takes cur[u+1] of lane 0
-            const uint4 give = (lane == 0 && u + 1 < U) ? cur[u + 1 < U ? u + 1 : u] : cur[u]; // (index clamped for the compiler only)
-            uint4 nxt;
-            nxt.x = __shfl_sync(0xffffffffu, give.x, (lane + 1) & 31);
-            nxt.y = __shfl_sync(0xffffffffu, give.y, (lane + 1) & 31);
-            nxt.z = __shfl_sync(0xffffffffu, give.z, (lane + 1) & 31);
-            nxt.w = __shfl_sync(0xffffffffu, give.w, (lane + 1) & 31);
-            const long long slot = u * 32 + (long long)lane, j = base + slot;
-            if (slot < run && j >= 0 && j < nv) {
-                const uint4 out = shift_pair(cur[u], nxt, m);
+            for (int u = 0; u < U; ++u) {
+                if (NSRC == 1) {
+                    cur[u] = val[u][0];
+                } else {
+                    Acc<T> a;
+                    a.set(val[u][0]);
 #pragma unroll
-                for (int q = 0; q < NDST; ++q) st_v4(d[q] + j, out);
+                    for (int p = 1; p < NSRC; ++p) a.add(val[u][p]);
+                    cur[u] = a.pack();
+                }
+            }
+            // rows row0-1 (carried), row0 .. row0+U-2: each is complete now that its successor row is summed
+#pragma unroll
+            for (int u = -1; u < U - 1; ++u) {
+                const uint4 mine = u < 0 ? carry : cur[u < 0 ? 0 : u];
+                const uint4 succ = cur[u + 1];
+                // lane l takes `mine` of lane l+1; lane 31 takes `succ` of lane 0
+                const uint4 give = lane == 0 ? succ : mine;
+                uint4 nxt;
+                nxt.x = __shfl_sync(0xffffffffu, give.x, (lane + 1) & 31);
+                nxt.y = __shfl_sync(0xffffffffu, give.y, (lane + 1) & 31);
+                nxt.z = __shfl_sync(0xffffffffu, give.z, (lane + 1) & 31);
+                nxt.w = __shfl_sync(0xffffffffu, give.w, (lane + 1) & 31);
+                const long long slot = (row0 + u) * 32 + (long long)lane, j = base + slot;
+                if (row0 + u >= 0 && slot < run && j >= 0 && j < nv) {
+                    const uint4 out = shift_pair(mine, nxt, m);
+#pragma unroll
+                    for (int q = 0; q < NDST; ++q) st_v4(d[q] + j, out);
+                }
+            }
+            carry = cur[U - 1];
+            // the window's (or the data's) last row has no successor row: its lanes 0..30 finish among themselves
+            const bool last_step = row0 + U >= rows || base + (row0 + U) * 32 > nv;
+            if (last_step) {
+                uint4 nxt;
+                nxt.x = __shfl_sync(0xffffffffu, carry.x, (lane + 1) & 31);
+                nxt.y = __shfl_sync(0xffffffffu, carry.y, (lane + 1) & 31);
+                nxt.z = __shfl_sync(0xffffffffu, carry.z, (lane + 1) & 31);
+                nxt.w = __shfl_sync(0xffffffffu, carry.w, (lane + 1) & 31);
+                const long long slot = (row0 + U - 1) * 32 + (long long)lane, j = base + slot;
+                if (lane < 31u && slot < run && j >= 0 && j < nv) {
+                    const uint4 out = shift_pair(carry, nxt, m);
+#pragma unroll
+                    for (int q = 0; q < NDST; ++q) st_v4(d[q] + j, out);
+                }
             }
         }
     }

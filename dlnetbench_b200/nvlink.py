@@ -71,11 +71,10 @@ class LinkCounters:
         import subprocess
 
         txt = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(self.index)], capture_output=True, text=True, timeout=20).stdout
-        tx = sum(int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", txt))
-        rx = sum(int(x) for x in re.findall(r"Data Rx:\s*(\d+)\s*KiB", txt))
-        if not re.search(r"Data Tx", txt):
-            raise RuntimeError("nvidia-smi nvlink -gt d printed no counters: " + txt[:120].replace("\n", " "))
-        return {"data_tx": tx * 1024, "data_rx": rx * 1024}
+        txs, rxs = re.findall(r"Data Tx:\s*(\d+)\s*KiB", txt), re.findall(r"Data Rx:\s*(\d+)\s*KiB", txt)
+        if not txs or not rxs:  # this pool prints "Data Tx: N/A" for every link: the counters are not exposed
+            raise RuntimeError("nvidia-smi nvlink -gt d shows no readable counter: " + " ".join(txt.split())[:100])
+        return {"data_tx": sum(int(x) for x in txs) * 1024, "data_rx": sum(int(x) for x in rxs) * 1024}
 
     def settle(self) -> dict:
         """Read after the counters had time to catch up with finished work."""
