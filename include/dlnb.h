@@ -195,6 +195,9 @@ uint64_t dlnb_launch_count(void);
 /* ---- device timing -------------------------------------------------------------
  * Added (no reference counterpart; the reference only has host timers,
  * ccutils CCUTILS_MPI_TIMER_*): cudaEvent pair spanning both streams. */
+/* With more than one rank dlnb_iter_begin / dlnb_batch_begin are COLLECTIVE over the world (every rank must call them the same
+ * number of times): unless dlnb_set("align_iterations", 0), they enqueue one device-side flag barrier between all ranks so
+ * that the iteration starts on all GPUs within a flag round trip (a rank that never arrives trips the 30 s watchdog). */
 int dlnb_iter_begin(void);
 int dlnb_iter_end(float *ms);
 /* like dlnb_iter_begin, but the timer starts on the communication stream behind everything
@@ -203,7 +206,8 @@ int dlnb_iter_end(float *ms);
 int dlnb_batch_begin(void);
 /* Contention measurements: like dlnb_batch_begin / dlnb_iter_end, but the collectives issued between the two
  * calls do NOT wait for the compute stream — emulated compute enqueued before keeps running beside them — and
- * the end does not wait for it either. */
+ * the end does not wait for it either. Always pair the two calls: until dlnb_batch_end() collectives keep ignoring the
+ * compute stream. */
 int dlnb_batch_begin_concurrent(double gate_us); /* gate_us > 0: a sleeping warp holds the stream that long while the host queues */
 int dlnb_batch_end(float *ms);
 /* device time of the most recent collective recorded in `slot` (ms); slot -1 = the most
